@@ -1,0 +1,336 @@
+"""Golden-vector generator: runs the UNMODIFIED reference (via oracle/ref_shim.py) in THIS
+container and writes small fixtures to tests/golden/.  Test infrastructure only.
+
+    python oracle/gen_golden.py            # regenerate everything (one subprocess per scenario)
+    python oracle/gen_golden.py --only rollout_a1_rk4
+
+Why subprocesses: `RaceCar.scan_simulator/cosines/scan_angles/side_distances` are class-level
+statics (reference base_classes.py:63-66,116) so one process can hold one (beams, fov) only.
+
+What each fixture pins (reference file:line):
+  scans_*        ScanSimulator2D.scan(pose, None)            laser_models.py:429 -> get_scan :149 -> trace_ray :107
+  rollout_*      F110Env.reset/step                          f110_env.py:261,304 -> Simulator.step base_classes.py:546
+                 (states, collisions, collision_idx, toggles, lap counters, scans at sampled steps)
+  waypoint_follow  examples/waypoint_follow.py main loop (BASELINE config 1), action stream recorded
+"""
+import argparse
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(HERE)
+GOLDEN = os.path.join(REPO, "tests", "golden")
+REF = "/root/reference"
+MAPS = {
+    "example_map": REF + "/examples/example_map",
+    "berlin": REF + "/gym/f110_gym/envs/maps/berlin",
+    "skirk": REF + "/gym/f110_gym/envs/maps/skirk",
+    "vegas": REF + "/gym/f110_gym/envs/maps/vegas",
+    "stata_basement": REF + "/gym/f110_gym/envs/maps/stata_basement",
+}
+FOVS = {"2pi": 2 * np.pi, "4p7": 4.7}
+
+
+def _ref():
+    sys.path.insert(0, HERE)
+    import ref_shim
+    return ref_shim.install()
+
+
+def waypoint_poses(n, offset=0.0):
+    """n start poses on the example_map raceline: rows k*R/n, (x, y, psi+pi/2)."""
+    wp = np.loadtxt(REF + "/examples/example_waypoints.csv", delimiter=";", skiprows=3)
+    idx = (np.arange(n) * wp.shape[0]) // n
+    poses = np.stack([wp[idx, 1], wp[idx, 2], wp[idx, 3] + np.pi / 2], axis=1)
+    if offset:
+        poses[:, 0] -= offset * np.cos(poses[:, 2])
+        poses[:, 1] -= offset * np.sin(poses[:, 2])
+    return poses
+
+
+# ----------------------------------------------------------------------------- scans
+def gen_scans(map_name, fov_name, beams=1080, n_poses=20):
+    _ref()
+    from f110_gym.envs.laser_models import ScanSimulator2D
+    fov = FOVS[fov_name]
+    sim = ScanSimulator2D(beams, fov)
+    sim.set_map(MAPS[map_name] + ".yaml", ".png")
+    rng = np.random.default_rng(7)
+    free = np.argwhere(sim.dt > 0.3)
+    pick = free[rng.choice(free.shape[0], n_poses, replace=False)]
+    # cell centre -> world (origin yaw is 0 for every bundled map)
+    x = sim.orig_x + (pick[:, 1] + rng.uniform(0, 1, n_poses)) * sim.map_resolution
+    y = sim.orig_y + (pick[:, 0] + rng.uniform(0, 1, n_poses)) * sim.map_resolution
+    th = rng.uniform(-2 * np.pi, 4 * np.pi, n_poses)   # includes negative / >2pi yaw (wrap path)
+    if map_name == "example_map":
+        # most free cells of example_map lie outside the track: put 3/4 of the poses on the raceline
+        wp = np.loadtxt(REF + "/examples/example_waypoints.csv", delimiter=";", skiprows=3)
+        k = (3 * n_poses) // 4
+        rows = rng.choice(wp.shape[0], k, replace=False)
+        x[:k] = wp[rows, 1] + rng.uniform(-0.4, 0.4, k)
+        y[:k] = wp[rows, 2] + rng.uniform(-0.4, 0.4, k)
+    poses = np.stack([x, y, th], axis=1)
+    # edge cases: outside the map (xy_2_rc -> (-1,-1), laser_models.py:79-81), on an obstacle,
+    # exactly on the map origin, yaw exactly 0 and fov/2
+    occ = np.argwhere(sim.dt == 0.0)[0]
+    extra = np.array([
+        [sim.orig_x - 5.0, sim.orig_y - 5.0, 0.3],
+        [sim.orig_x + sim.map_width * sim.map_resolution + 1.0, sim.orig_y + 1.0, 2.0],
+        [sim.orig_x + (occ[1] + 0.5) * sim.map_resolution, sim.orig_y + (occ[0] + 0.5) * sim.map_resolution, 1.0],
+        [sim.orig_x, sim.orig_y, 0.0],
+        [x[0], y[0], 0.0],
+        [x[0], y[0], fov / 2.0],
+    ])
+    poses = np.concatenate([poses, extra], axis=0)
+    scans = np.stack([sim.scan(p, None) for p in poses])
+    out = os.path.join(GOLDEN, "scans_%s_%s_b%d.npz" % (map_name, fov_name, beams))
+    np.savez_compressed(out, poses=poses, scans=scans, fov=fov, beams=beams, map=map_name)
+    print("wrote", out, scans.shape)
+
+
+# ----------------------------------------------------------------------------- rollouts
+def _rollout(tag, map_name, num_agents, integrator_name, fov_name, n_envs, n_steps, poses0, actions,
+             scan_every, seed=12345, params=None):
+    gym = _ref()
+    from f110_gym.envs.base_classes import Integrator
+    integ = getattr(Integrator, integrator_name)
+    fov = FOVS[fov_name]
+    A = num_agents
+    S = np.zeros((n_envs, n_steps + 1, A, 7))
+    coll = np.zeros((n_envs, n_steps + 1, A))
+    cidx = np.zeros((n_envs, n_steps + 1, A))
+    tog = np.zeros((n_envs, n_steps + 1, A))
+    lapc = np.zeros((n_envs, n_steps + 1, A))
+    lapt = np.zeros((n_envs, n_steps + 1, A))
+    done = np.zeros((n_envs, n_steps + 1), dtype=bool)
+    obs_pose = np.zeros((n_envs, n_steps + 1, A, 5))   # poses_x, poses_y, poses_theta, linear_vels_x, ang_vels_z
+    scan_steps = np.array(sorted(set([0, 1, 2] + list(range(0, n_steps + 1, scan_every)))))
+    scans = np.zeros((n_envs, scan_steps.size, A, 1080))
+    scan_sum = np.zeros((n_envs, n_steps + 1, A))
+    scan_min = np.zeros((n_envs, n_steps + 1, A))
+    kw = dict(map=MAPS[map_name], map_ext=".png", num_agents=A, timestep=0.01, integrator=integ, fov=fov, seed=seed)
+    if params is not None:
+        kw["params"] = params
+    for e in range(n_envs):
+        env = gym.make("f110_gym:f110-v0", **kw)
+
+        def rec(t, obs, d):
+            for a in range(A):
+                S[e, t, a] = env.sim.agents[a].state
+                obs_pose[e, t, a] = [obs["poses_x"][a], obs["poses_y"][a], obs["poses_theta"][a],
+                                     obs["linear_vels_x"][a], obs["ang_vels_z"][a]]
+                scan_sum[e, t, a] = obs["scans"][a].sum()
+                scan_min[e, t, a] = obs["scans"][a].min()
+            coll[e, t] = obs["collisions"]
+            cidx[e, t] = env.sim.collision_idx
+            tog[e, t] = env.toggle_list
+            lapc[e, t] = obs["lap_counts"]
+            lapt[e, t] = obs["lap_times"]
+            done[e, t] = d
+            k = np.searchsorted(scan_steps, t)
+            if k < scan_steps.size and scan_steps[k] == t:
+                for a in range(A):
+                    scans[e, k, a] = obs["scans"][a]
+
+        obs, r, d, info = env.reset(poses0[e].copy())
+        rec(0, obs, d)
+        for t in range(n_steps):
+            obs, r, d, info = env.step(actions[t, e].copy())
+            rec(t + 1, obs, d)
+    out = os.path.join(GOLDEN, tag + ".npz")
+    np.savez_compressed(out, map=map_name, num_agents=A, integrator=integrator_name, fov=fov, seed=seed,
+                        poses0=poses0, actions=actions, states=S, obs_pose=obs_pose, collisions=coll,
+                        collision_idx=cidx, toggles=tog, lap_counts=lapc, lap_times=lapt, done=done,
+                        scan_steps=scan_steps, scans=scans, scan_sum=scan_sum, scan_min=scan_min)
+    print("wrote", out, "collided envs:", int((coll.max(axis=(1, 2)) > 0).sum()), "of", n_envs,
+          "max toggles", tog.max())
+
+
+def _random_actions(n_steps, n_envs, A, seed=2024, speed_hi=8.0, hold=1):
+    rng = np.random.default_rng(seed)
+    n_draw = (n_steps + hold - 1) // hold
+    steer = rng.uniform(-0.4189, 0.4189, (n_draw, n_envs, A))
+    speed = rng.uniform(0.0, speed_hi, (n_draw, n_envs, A))
+    act = np.stack([steer, speed], axis=-1)
+    return np.repeat(act, hold, axis=0)[:n_steps]
+
+
+def gen_rollout_a1_rk4():
+    n, T = 8, 1000
+    poses0 = waypoint_poses(n)[:, None, :]
+    _rollout("rollout_a1_rk4", "example_map", 1, "RK4", "2pi", n, T, poses0, _random_actions(T, n, 1), 100)
+
+
+def gen_rollout_a1_rk4_smooth():
+    # piecewise-constant actions (held 25 steps): cars build speed, leave the kinematic regime,
+    # some survive long enough to toggle the lap zone
+    n, T = 6, 1000
+    poses0 = waypoint_poses(n)[:, None, :]
+    act = _random_actions(T, n, 1, seed=99, speed_hi=6.0, hold=25)
+    act[..., 0] *= 0.35
+    _rollout("rollout_a1_rk4_smooth", "example_map", 1, "RK4", "2pi", n, T, poses0, act, 250)
+
+
+def gen_rollout_a1_euler():
+    n, T = 4, 400
+    rng = np.random.default_rng(5)
+    poses0 = np.array([[0.0, 0.0, 1.2], [0.0, 0.0, -1.0], [0.3, -0.2, 4.5], [-0.2, 0.1, 0.2]])[:, None, :]
+    act = _random_actions(T, n, 1, seed=11, speed_hi=5.0, hold=10)
+    _rollout("rollout_a1_euler_berlin", "berlin", 1, "Euler", "4p7", n, T, poses0, act, 100, seed=777)
+
+
+def gen_rollout_a2():
+    # chaser 1.5 m behind the leader with a lateral offset; GJK + opponent ray-cast fire
+    n, T = 8, 600
+    rng = np.random.default_rng(4)
+    lead = waypoint_poses(n)
+    chase = lead.copy()
+    lat = rng.uniform(-0.3, 0.3, n)
+    chase[:, 0] += -1.5 * np.cos(lead[:, 2]) - lat * np.sin(lead[:, 2])
+    chase[:, 1] += -1.5 * np.sin(lead[:, 2]) + lat * np.cos(lead[:, 2])
+    poses0 = np.stack([lead, chase], axis=1)
+    act = np.zeros((T, n, 2, 2))
+    steer = rng.uniform(-0.15, 0.15, (T // 20 + 1, n, 2)).repeat(20, axis=0)[:T]
+    act[..., 0] = steer
+    act[:, :, 0, 1] = rng.uniform(0.0, 4.0, (T // 20 + 1, n)).repeat(20, axis=0)[:T]
+    act[:, :, 1, 1] = rng.uniform(2.0, 8.0, (T // 20 + 1, n)).repeat(20, axis=0)[:T]
+    _rollout("rollout_a2_rk4", "example_map", 2, "RK4", "2pi", n, T, poses0, act, 100)
+
+
+def gen_rollout_a3():
+    # three agents side by side on skirk: collision_multiple over 3 pairs (collision_models.py:185)
+    n, T = 3, 300
+    rng = np.random.default_rng(8)
+    base = np.array([[0.0, 0.0, 1.5], [0.2, 0.1, 1.0], [-0.1, 0.0, 2.0]])
+    poses0 = np.zeros((n, 3, 3))
+    for e in range(n):
+        th = base[e, 2]
+        for a in range(3):
+            off = (a - 1) * 0.45
+            poses0[e, a] = [base[e, 0] - off * np.sin(th), base[e, 1] + off * np.cos(th) , th + 0.05 * a]
+    act = np.zeros((T, n, 3, 2))
+    act[..., 0] = rng.uniform(-0.2, 0.2, (T // 15 + 1, n, 3)).repeat(15, axis=0)[:T]
+    act[..., 1] = rng.uniform(0.5, 4.0, (T // 15 + 1, n, 3)).repeat(15, axis=0)[:T]
+    _rollout("rollout_a3_skirk", "skirk", 3, "RK4", "2pi", n, T, poses0, act, 100, seed=31)
+
+
+def gen_waypoint_follow():
+    """BASELINE config 1: examples/waypoint_follow.py with render() skipped (GL unavailable on this box)."""
+    gym = _ref()
+    sys.path.insert(0, REF + "/examples")
+    import yaml
+    from argparse import Namespace
+    import waypoint_follow as wf
+    from f110_gym.envs.base_classes import Integrator
+    os.chdir(REF + "/examples")
+    with open("config_example_map.yaml") as f:
+        conf = Namespace(**yaml.load(f, Loader=yaml.FullLoader))
+    planner = wf.PurePursuitPlanner(conf, 0.17145 + 0.15875)
+    env = gym.make("f110_gym:f110-v0", map=conf.map_path, map_ext=conf.map_ext, num_agents=1, timestep=0.01,
+                   integrator=Integrator.RK4)
+    obs, r, done, info = env.reset(np.array([[conf.sx, conf.sy, conf.stheta]]))
+    acts, poses, vels, laps, lapt, tog = [], [], [], [], [], []
+    poses.append([obs["poses_x"][0], obs["poses_y"][0], obs["poses_theta"][0]])
+    while not done:
+        speed, steer = planner.plan(obs["poses_x"][0], obs["poses_y"][0], obs["poses_theta"][0],
+                                    0.82461887897713965, 1.375)
+        obs, r, done, info = env.step(np.array([[steer, speed]]))
+        acts.append([steer, speed])
+        poses.append([obs["poses_x"][0], obs["poses_y"][0], obs["poses_theta"][0]])
+        vels.append(obs["linear_vels_x"][0])
+        laps.append(obs["lap_counts"][0]); lapt.append(obs["lap_times"][0]); tog.append(env.toggle_list[0])
+    out = os.path.join(GOLDEN, "waypoint_follow.npz")
+    np.savez_compressed(out, actions=np.array(acts), poses=np.array(poses), vels=np.array(vels),
+                        lap_counts=np.array(laps), lap_times=np.array(lapt), toggles=np.array(tog),
+                        final_collision=obs["collisions"][0], final_scan=obs["scans"][0],
+                        start=np.array([conf.sx, conf.sy, conf.stheta]))
+    print("wrote", out, "steps", len(acts), "lap time", lapt[-1], "collision", obs["collisions"][0])
+
+
+def gen_kats():
+    """Known-answer inputs of the reference's embedded unit tests, evaluated by the reference itself."""
+    _ref()
+    from f110_gym.envs import collision_models as cm, dynamic_models as dm, laser_models as lm
+    out = {}
+    # CollisionTests.setUp / test_multiple_collisions (collision_models.py:272-324)
+    np.random.seed(1234)
+    v1 = np.asarray([[4, 11.], [5, 5], [9, 9], [10, 10]])
+    bodies = [v1 + np.random.normal(size=v1.shape) / 100. for _ in range(6)] + [v1 + 10.]
+    allv = np.stack(bodies)
+    c, ci = cm.collision_multiple(allv)
+    out.update(gjk_bodies=allv, gjk_collisions=c, gjk_collision_idx=ci)
+    # 1000 jittered pairs (test_random_collision :306-311) + far/near separated pairs
+    rng = np.random.default_rng(3)
+    pa = v1 + rng.normal(size=(1000, 4, 2)) / 100.
+    pb = v1 + rng.normal(size=(1000, 4, 2)) / 100.
+    pb[500:] += rng.uniform(-8, 8, size=(500, 1, 2))
+    out.update(gjk_pairs_a=pa, gjk_pairs_b=pb,
+               gjk_pairs_hit=np.array([cm.collision(np.ascontiguousarray(pa[i]), np.ascontiguousarray(pb[i])) for i in range(1000)]))
+    # car rectangles at random relative poses (get_vertices :238 + collision :114)
+    poses_a = np.concatenate([rng.uniform(-1, 1, (2000, 2)), rng.uniform(-4, 4, (2000, 1))], axis=1)
+    poses_b = np.concatenate([rng.uniform(-1, 1, (2000, 2)), rng.uniform(-4, 4, (2000, 1))], axis=1)
+    poses_b[:50] = poses_a[:50]                       # identical centres: d==0 branch (:133-134)
+    poses_b[50:100, 2] = poses_a[50:100, 2]           # parallel
+    va = np.stack([cm.get_vertices(p, 0.58, 0.31) for p in poses_a])
+    vb = np.stack([cm.get_vertices(p, 0.58, 0.31) for p in poses_b])
+    hit = np.array([cm.collision(np.ascontiguousarray(va[i]), np.ascontiguousarray(vb[i])) for i in range(2000)])
+    out.update(car_poses_a=poses_a, car_poses_b=poses_b, car_verts_a=va, car_verts_b=vb, car_hit=hit)
+    # opponent ray-cast (laser_models.py:319) on a flat 30 m scan
+    fov = 2 * np.pi
+    angles = np.array([-fov / 2. + i * (fov / 1079) for i in range(1080)])
+    rc_scans = []
+    ego = np.array([0.3, -0.2, 0.7])
+    for i in range(64):
+        scan = np.full(1080, 30.0)
+        rc_scans.append(lm.ray_cast(ego, scan, angles, va[i] + np.array([ego[0], ego[1]])))
+    out.update(rc_ego=ego, rc_scans=np.stack(rc_scans), rc_angles=angles)
+    # check_ttc_jit (laser_models.py:189)
+    # dynamics known answers: evaluate the RHS on random states (both regimes) and pid
+    p = [1.0489, 4.718, 5.4562, 0.15875, 0.17145, 0.074, 3.74, 0.04712, -0.4189, 0.4189, -3.2, 3.2, 7.319, 9.51, -5.0, 20.0]
+    X = rng.uniform(-1, 1, (512, 7)) * np.array([10, 10, 0.45, 12, 6.3, 3, 0.5])
+    X[:64, 3] = rng.uniform(-0.6, 0.6, 64)
+    U = rng.uniform(-1, 1, (512, 2)) * np.array([4.0, 12.0])
+    F = np.stack([dm.vehicle_dynamics_st(X[i], U[i], *p) for i in range(512)])
+    pid_in = rng.uniform(-1, 1, (512, 4)) * np.array([10, 0.5, 10, 0.5])
+    pid_out = np.array([dm.pid(s[0], s[1], s[2], s[3], 3.2, 9.51, 20.0, -5.0) for s in pid_in])
+    out.update(dyn_params=np.array(p), dyn_x=X, dyn_u=U, dyn_f=F, pid_in=pid_in, pid_out=pid_out)
+    path = os.path.join(GOLDEN, "kats.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, "car hits", int(hit.sum()))
+
+
+SCENARIOS = {
+    "kats": gen_kats,
+    "rollout_a1_rk4": gen_rollout_a1_rk4,
+    "rollout_a1_rk4_smooth": gen_rollout_a1_rk4_smooth,
+    "rollout_a1_euler": gen_rollout_a1_euler,
+    "rollout_a2": gen_rollout_a2,
+    "rollout_a3": gen_rollout_a3,
+    "waypoint_follow": gen_waypoint_follow,
+}
+for _m in MAPS:
+    for _f in FOVS:
+        SCENARIOS["scans_%s_%s" % (_m, _f)] = (lambda m=_m, f=_f: gen_scans(m, f))
+SCENARIOS["scans_example_map_2pi_b270"] = lambda: gen_scans("example_map", "2pi", beams=270, n_poses=12)
+SCENARIOS["scans_example_map_2pi_b2160"] = lambda: gen_scans("example_map", "2pi", beams=2160, n_poses=6)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", nargs="*", default=None)
+    ap.add_argument("--worker", default=None)
+    args = ap.parse_args()
+    os.makedirs(GOLDEN, exist_ok=True)
+    if args.worker:
+        SCENARIOS[args.worker]()
+        return
+    names = args.only or list(SCENARIOS)
+    for n in names:
+        subprocess.run([sys.executable, os.path.abspath(__file__), "--worker", n], check=True)
+
+
+if __name__ == "__main__":
+    main()
