@@ -1,0 +1,350 @@
+#!/usr/bin/env python
+"""bench.py -- agent-steps/s of the batched F1TENTH step (1080-beam lidar) on N B200s.
+
+    python bench.py [--gpus N --steps K --warmup W] [--workload config3|config2|config4] [--impl reference]
+
+One "step" = one pass of the hot path (dynamics -> lidar -> iTTC -> [GJK, opponent ray-cast] -> laps) over
+every env of the batch.  Workloads follow BASELINE.json `configs`:
+  config3 (default; the one the metric is quoted on): 2^20 single-agent envs per GPU on example_map, fp32 lidar
+           fast path, Philox noise, auto-reset from a raceline pose pool, random actions resident in HBM.
+  config2: 4096 single-agent envs, fp64 parity path (numpy noise rows).
+  config4: 65536 two-agent head-to-head envs, fp64 parity path.
+Multi-GPU: pure env sharding, one process per GPU (torchrun), no collective inside step; weak scaling
+(per-GPU env count fixed).  Timing: CUDA events on the launching stream, max over ranks.
+
+`--impl reference` times the CPU restatement of the reference (oracle/, all host threads) on a bounded
+sample of the same workload; the reference itself is pure Python + Numba and does not travel to the box.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+WORKLOADS = {
+    # name: (envs per GPU, agents, dtype, noise, auto_reset)
+    "config3": (1 << 20, 1, "fp32", "philox", True),
+    "config2": (4096, 1, "fp64", "numpy", False),
+    "config4": (65536, 2, "fp64", "numpy", False),
+}
+L2_FLUSH_NOTE = "per-step working set (scans %.2f GB) exceeds the 126 MB L2; EDT (%.1f MB) stays L2-resident by design"
+
+
+def load_peaks():
+    p = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device_index):
+        self.idx = device_index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line)
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9 or not f[0].isdigit() or int(f[0]) != self.idx:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_poses(n_envs, agents):
+    from red_gym_b200.host import raceline_poses
+    lead = raceline_poses(n_envs)
+    if agents == 1:
+        return lead[:, None, :]
+    rng = np.random.default_rng(4)
+    out = [lead]
+    for a in range(1, agents):
+        lat = rng.uniform(-0.3, 0.3, n_envs)
+        c = lead.copy()
+        c[:, 0] += -1.5 * a * np.cos(lead[:, 2]) - lat * np.sin(lead[:, 2])
+        c[:, 1] += -1.5 * a * np.sin(lead[:, 2]) + lat * np.cos(lead[:, 2])
+        out.append(c)
+    return np.stack(out, axis=1)
+
+
+def action_bank(torch, n_envs, agents, device, n_bank, seed):
+    """Synthetic action stream: steer ~ U(-0.4189, 0.4189), speed ~ U(0, 8); a bank of tensors
+    generated before the timed region so that inputs are resident in HBM when it starts."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    bank = []
+    for _ in range(n_bank):
+        a = torch.rand((n_envs, agents, 2), generator=g, device=device, dtype=torch.float64)
+        a[..., 0] = (a[..., 0] * 2 - 1) * 0.4189
+        a[..., 1] = a[..., 1] * 8.0
+        bank.append(a.contiguous())
+    return bank
+
+
+def l2_gather_peak(torch, device):
+    """Measured L2 gather bandwidth of this GPU: 4-byte random gathers from a 10 MB table (L2-resident,
+    same footprint as the fp32 EDT of example_map), counted at 32-byte sector granularity and as useful bytes."""
+    n_tab = 2560 * 1024
+    tab = torch.rand(n_tab, device=device, dtype=torch.float32)
+    idx = torch.randint(0, n_tab, (1 << 26,), device=device, dtype=torch.int32)
+    out = torch.empty(1 << 26, device=device, dtype=torch.float32)
+    for _ in range(2):
+        torch.index_select(tab, 0, idx, out=out)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        torch.index_select(tab, 0, idx, out=out)
+    e1.record()
+    torch.cuda.synchronize()
+    gathers_per_s = 5 * (1 << 26) / (e0.elapsed_time(e1) * 1e-3)
+    return {"gathers_per_s": gathers_per_s, "useful_GBps": gathers_per_s * 4 / 1e9, "sector_GBps": gathers_per_s * 32 / 1e9,
+            "how": "torch.index_select, 2^26 random 4-byte gathers from a 10 MB table (includes the index read and output write)"}
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from red_gym_b200 import BatchF110Env, MAPS_DIR
+    from red_gym_b200.host import raceline_poses
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    n_envs, agents, dtype, noise, auto = WORKLOADS[args.workload]
+    if args.envs:
+        n_envs = args.envs
+    if args.dtype:
+        dtype = args.dtype
+        noise = "numpy" if dtype == "fp64" else "philox"
+    B = 1080
+    env = BatchF110Env(num_envs=n_envs, device=local, dtype=dtype, noise=noise, num_agents=agents, auto_reset=True,
+                       reset_poses=make_poses(1024, agents), raycast_variant=args.variant,
+                       map=os.path.join(MAPS_DIR, "example_map"), seed=12345 + rank)
+    # every workload auto-resets here: a throughput run must keep cars alive (the parity tests cover no-reset runs)
+    env.reset(make_poses(n_envs, agents))
+    bank = action_bank(torch, n_envs, agents, device, 8, 2024 + rank)
+    K, W = args.steps, args.warmup
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(W):
+        env.step(bank[i % len(bank)])
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = env.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(K):
+        env.step(bank[i % len(bank)])
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = env.launch_count - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    total_agent_steps = float(n_envs) * agents * K * world
+    value = total_agent_steps / (ms_max * 1e-3)
+
+    # ---- roofline of the dominant kernel (ray-cast), measured live with CUDA events on the launching stream
+    env.enable_timing(True)
+    rc_ms = []
+    for i in range(max(3, min(K, 10))):
+        env.step(bank[i % len(bank)])
+        rc_ms.append(env.last_raycast_ms())
+    env.enable_timing(False)
+    env.count_lookups(True)
+    n_cnt = 3
+    for i in range(n_cnt):
+        env.step(bank[i % len(bank)])
+    torch.cuda.synchronize()
+    lookups_per_scan = env.lookups() / float(n_cnt * n_envs * agents)
+    env.count_lookups(False)
+    esz = 4 if dtype == "fp32" else 8
+    bytes_per_scan = lookups_per_scan * esz + B * esz            # L*sizeof(edt_t) + B*sizeof(scan_t)
+    rc_avg_ms = float(np.mean(rc_ms))
+    achieved = bytes_per_scan * n_envs * agents / (rc_avg_ms * 1e-3) / 1e9
+    peak, peak_src = load_peaks()
+    traffic = None
+    tp = os.path.join(REPO, "profiles", "roofline_traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get(args.workload)
+    roofline = {"kernel": "k_raycast32" if dtype == "fp32" else "k_raycast64", "bound": "hbm", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "launch_ms": rc_avg_ms, "lookups_per_scan": lookups_per_scan, "bytes_per_scan": bytes_per_scan,
+                "scans_per_launch": n_envs * agents, "raycast_share_of_step": rc_avg_ms / (ms_max / K)}
+    l2 = None
+    if rank == 0:
+        l2 = l2_gather_peak(torch, device)
+        l2["achieved_lookups_per_s"] = lookups_per_scan * n_envs * agents / (rc_avg_ms * 1e-3)
+        l2["frac_of_gather_peak"] = l2["achieved_lookups_per_s"] / l2["gathers_per_s"]
+
+    # ---- e2e: the same step through f110_step_host with HOST buffers (H2D actions, D2H observation every step)
+    e2e = None
+    if not args.no_e2e:
+        NA = n_envs * agents
+        act_h = torch.zeros((n_envs, agents, 2), dtype=torch.float64).pin_memory()
+        obs_h = torch.zeros((10, n_envs, agents), dtype=torch.float64).pin_memory()
+        scans_h = torch.zeros((n_envs, agents, B), dtype=torch.float32 if dtype == "fp32" else torch.float64).pin_memory()
+        done_h = torch.zeros((n_envs,), dtype=torch.uint8).pin_memory()
+        act_h.copy_(bank[0])
+        Ke = max(2, min(K, args.e2e_steps))
+        for _ in range(2):
+            env.step_host(act_h, obs_h, scans_h, done_h)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            env.step_host(act_h, obs_h, scans_h, done_h)
+        torch.cuda.synchronize()
+        t_e = time.perf_counter() - t0
+        te = torch.tensor([t_e], device=device, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": float(n_envs) * agents * Ke * world / float(te.item()), "unit": "agent-steps/s",
+               "h2d_bytes_per_step": act_h.numel() * 8 * world,
+               "d2h_bytes_per_step": (obs_h.numel() * 8 + scans_h.numel() * scans_h.element_size() + done_h.numel()) * world,
+               "steps": Ke, "api": "f110_step_host (C ABI, pinned host buffers, full observation incl. scans copied back)"}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu_baseline = cpu_reference(args.workload, seconds=12.0)
+    if rank == 0:
+        scan_gb = n_envs * agents * B * esz / 1e9
+        line = {"metric": "agent-steps/sec (1080-beam lidar)", "value": value, "unit": "agent-steps/s", "n_gpus": world,
+                "steps": K, "warmup": W, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32" if dtype == "fp32" else "f64", "data": "synthetic",
+                "config": {"workload": args.workload, "envs_per_gpu": n_envs, "agents": agents, "beams": B, "map": "example_map",
+                           "integrator": "RK4", "noise": noise, "auto_reset": True, "parallelism": "env-shard x%d" % world,
+                           "raycast_variant": args.variant,
+                           "l2_flush": L2_FLUSH_NOTE % (scan_gb, 10.24 if dtype == "fp32" else 20.48)},
+                "roofline": roofline, "l2_roofline": l2, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
+                "clocks": clocks}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_reference(workload, seconds=12.0, nthreads=0):
+    """The CPU restatement of the reference (oracle/, pthreads over envs) on a bounded sample of the workload."""
+    sys.path.insert(0, os.path.join(REPO, "oracle"))
+    import f110_oracle as fo
+    from red_gym_b200 import MAPS_DIR
+    _, agents, _, _, _ = WORKLOADS[workload]
+    cores = os.cpu_count() or 1
+    n = 64 * cores
+    poses = make_poses(n, agents)
+    env = fo.OracleEnv(n, agents, map=os.path.join(MAPS_DIR, "example_map"), nthreads=nthreads or cores, noise_rows=4096)
+    env.reset(poses)
+    rng = np.random.default_rng(2024)
+
+    def act():
+        return np.stack([rng.uniform(-0.4189, 0.4189, (n, agents)), rng.uniform(0, 8, (n, agents))], axis=-1)
+    for _ in range(3):
+        env.step(act())
+    steps, t0 = 0, time.perf_counter()
+    while time.perf_counter() - t0 < seconds:
+        env.step(act())
+        steps += 1
+        d = env.done.astype(bool)
+        if d.any():     # auto-reset like the GPU workload
+            env.reset(poses, mask=d)
+    dt = time.perf_counter() - t0
+    return {"value": n * agents * steps / dt, "unit": "agent-steps/s", "cores": nthreads or cores, "kind": "port",
+            "sample": "%d envs x %d steps (%.1f s) of %s on example_map, fp64, numpy noise rows, host auto-reset" % (n, steps, dt, workload)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    seconds = max(5.0, min(60.0, 1.5 * (args.steps + args.warmup)))
+    cb = cpu_reference(args.workload, seconds=seconds)
+    n_envs, agents, dtype, noise, auto = WORKLOADS[args.workload]
+    line = {"impl": "reference", "metric": "agent-steps/sec (1080-beam lidar)", "value": cb["value"], "unit": "agent-steps/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "agents": agents, "beams": 1080, "map": "example_map", "integrator": "RK4"},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
+    ap.add_argument("--envs", type=int, default=0, help="override envs per GPU")
+    ap.add_argument("--dtype", default=None, choices=["fp32", "fp64"])
+    ap.add_argument("--variant", type=int, default=2, help="raycast kernel variant (bit0 tiled fp64 EDT, bit1 lane refill)")
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

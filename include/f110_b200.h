@@ -1,0 +1,170 @@
+/*
+ * f110_b200.h -- C ABI of the B200-native batched F1TENTH simulator (libf110_b200.so).
+ *
+ * Drop-in boundary for ONE hot path of WE-Autopilot/red_gym: `Simulator.step` of the fork's
+ * f110_gym (dynamics -> 1080-beam EDT sphere-traced lidar -> iTTC -> GJK -> lap bookkeeping)
+ * over N independent environments.  The reference has no FFI of its own (pure Python + Numba,
+ * one env per process); the entry points below are what a binding for that path binds, each
+ * citing the reference interface it replaces (paths relative to gym/f110_gym/envs/).
+ *
+ * Conventions
+ *   - plain C: pointers + sizes only, no C++/torch types.  Every function returns 0 on success
+ *     or a negative f110_status; f110_last_error() gives the message (thread-local).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream).  Calls are
+ *     asynchronous on that stream unless stated; one handle per GPU, not thread-safe.
+ *   - the library owns all device memory; f110_get_buffers() exposes the device pointers so a
+ *     host framework (PyTorch, CuPy, ...) can wrap them without copies.
+ *   - layouts: per-agent arrays are [n_envs][n_agents] row-major, scans are
+ *     [n_envs][n_agents][n_beams]; the 7 state fields are SoA: state[field][n_envs*n_agents].
+ *   - there is NO CPU fallback: every entry point fails with F110_ERR_CUDA when no device works.
+ */
+#ifndef F110_B200_H
+#define F110_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define F110_ABI_VERSION 1
+#define F110_NUM_PARAMS 18   /* order: mu C_Sf C_Sr lf lr h m I s_min s_max sv_min sv_max v_switch a_max
+                                v_min v_max width length  (keys of the params dict, f110_env.py:128) */
+#define F110_MAX_AGENTS 32
+
+typedef enum {
+    F110_OK = 0,
+    F110_ERR_INVALID = -1,   /* bad argument (ValueError / IndexError on the Python side) */
+    F110_ERR_CUDA = -2,      /* CUDA runtime failure, incl. "no device" */
+    F110_ERR_STATE = -3,     /* call order: e.g. step before set_map (laser_models.py:445-446) */
+    F110_ERR_NOMEM = -4
+} f110_status;
+
+/* Integrator enum values of the reference (base_classes.py:40-42) */
+#define F110_INTEGRATOR_RK4 1
+#define F110_INTEGRATOR_EULER 2
+
+/* Arithmetic of the lidar path.  FP64 = parity path: fp64 EDT, same op order as the reference,
+ * no FMA contraction, noise rows supplied by the host (numpy PCG64 stream).  FP32 = fast path:
+ * fp32 EDT and scans, ray marching in cell units with FMA, Philox noise on the device;
+ * dynamics/GJK/lap logic stay fp64 in both. */
+#define F110_PRECISION_FP64 0
+#define F110_PRECISION_FP32 1
+
+/* Noise source */
+#define F110_NOISE_OFF 0      /* ScanSimulator2D.scan(pose, rng=None) */
+#define F110_NOISE_TABLE 1    /* host-generated rows: row k = k-th draw after reset (base_classes.py:202) */
+#define F110_NOISE_PHILOX 2   /* device counter-based N(0, std) keyed by (seed, env, agent, step, beam) */
+
+typedef struct f110_config {
+    int32_t abi_version;      /* F110_ABI_VERSION */
+    int32_t n_envs;           /* N independent copies of the reference env */
+    int32_t n_agents;         /* kwargs['num_agents'] (f110_env.py:132), <= F110_MAX_AGENTS */
+    int32_t n_beams;          /* ScanSimulator2D.num_beams (1080 through the env, base_classes.py:68) */
+    int32_t integrator;       /* F110_INTEGRATOR_* (f110_env.py:149-151) */
+    int32_t ego_idx;          /* f110_env.py:143 */
+    int32_t theta_dis;        /* 2000 (laser_models.py:360) */
+    int32_t precision;        /* F110_PRECISION_* */
+    int32_t noise_mode;       /* F110_NOISE_* */
+    int32_t auto_reset;       /* 0: like the reference (keep stepping after done); 1: a done env restarts from
+                                 the reset-pose pool on its next step (that step IS the reset's zero-action step) */
+    int32_t raycast_variant;  /* 0 = default; >0 selects an experimental kernel variant (bench only) */
+    int32_t reserved0;
+    double timestep;          /* f110_env.py:137 */
+    double fov;               /* f110_env.py:154-157 */
+    double eps;               /* 1e-4  (laser_models.py:360) */
+    double max_range;         /* 30.0 */
+    double ttc_thresh;        /* 0.005 (base_classes.py:113) */
+    double noise_std;         /* 0.01  (laser_models.py:429), used by F110_NOISE_PHILOX */
+    uint64_t seed;            /* f110_env.py:103 */
+} f110_config;
+
+typedef struct f110_sim f110_sim;
+
+/* Device pointers owned by the handle (valid until f110_destroy). */
+typedef struct f110_buffers {
+    double *state;          /* [7][N*A]: x, y, steer_angle, v, yaw, yaw_rate, slip (base_classes.py:95) */
+    double *obs_block;      /* [10][N*A] contiguous: the 7 state fields, then collisions, lap_times, lap_counts */
+    double *collisions;     /* [N][A] 0/1 (base_classes.py:480,582) */
+    double *collision_idx;  /* [N][A] -1 or partner (collision_models.py:197) */
+    double *lap_times;      /* [N][A] (f110_env.py:175) */
+    double *lap_counts;     /* [N][A] */
+    int32_t *toggles;       /* [N][A] toggle_list (f110_env.py:183) */
+    uint8_t *done;          /* [N] */
+    uint8_t *in_collision;  /* [N][A] iTTC flag (base_classes.py:250) */
+    void *scans;            /* [N][A][B] double (FP64) or float (FP32) */
+    double *cur_time;       /* [N] */
+    int64_t *noise_step;    /* [N] scans drawn since reset */
+    double *actions;        /* [N][A][2] device staging for f110_step_host (may also be written by the caller) */
+    int64_t *episode_count; /* [N] number of (auto-)resets */
+    uint64_t *lookups;      /* [1] EDT lookups counted when count_lookups was enabled */
+} f110_buffers;
+
+const char *f110_last_error(void);
+int f110_abi_version(void);
+int f110_device_count(void);
+
+/* F110Env.__init__ / Simulator.__init__ (f110_env.py:100-194, base_classes.py:459-490).
+ * device: CUDA device ordinal. */
+int f110_create(const f110_config *cfg, int device, f110_sim **out);
+int f110_destroy(f110_sim *sim);
+
+/* ScanSimulator2D.set_map (laser_models.py:383-427) after the host has loaded the image and
+ * built the EDT (host pointers; copied).  edt: [h][w] metres, row 0 = bottom row of the image. */
+int f110_set_map(f110_sim *sim, const double *edt, int32_t h, int32_t w, double resolution,
+                 double origin_x, double origin_y, double origin_c, double origin_s, void *stream);
+
+/* Trig tables (laser_models.py:379-381, theta_dis entries) and per-beam tables
+ * (base_classes.py:120-156, n_beams entries), computed by the host exactly as the reference does. */
+int f110_set_tables(f110_sim *sim, const double *sines, const double *cosines, const double *scan_angles,
+                    const double *beam_cosines, const double *side_distances, void *stream);
+
+/* Simulator.update_params (base_classes.py:507-527).  agent_idx < 0: all agents;
+ * agent_idx == n_agents: the construct-time {width,length} used by check_collision (:542). */
+int f110_set_params(f110_sim *sim, const double *params18, int32_t agent_idx, void *stream);
+
+/* F110_NOISE_TABLE: upload rows [first_row, first_row+n_rows) of the host noise stream
+ * (n_beams doubles each).  The table must cover max(noise_step)+1 before each step. */
+int f110_set_noise_rows(f110_sim *sim, const double *rows, int64_t first_row, int64_t n_rows, void *stream);
+
+/* Pool of start poses for auto_reset: [n_poses][n_agents][3] host doubles. */
+int f110_set_reset_pool(f110_sim *sim, const double *poses, int32_t n_poses, void *stream);
+
+/* F110Env.reset (f110_env.py:304-347): zero state, set poses, re-seed noise, then one zero-action
+ * step.  poses: host [N][A][3]; start_rot: host [N][4] row-major 2x2 rotation by -theta_ego as the
+ * reference computes it (:329), or NULL to compute it on the device; mask: host [N] bytes or NULL. */
+int f110_reset(f110_sim *sim, const double *poses, const double *start_rot, const uint8_t *mask, void *stream);
+
+/* F110Env.step -> Simulator.step (f110_env.py:261-302, base_classes.py:546-605) for all envs.
+ * actions_dev: DEVICE [N][A][2] doubles (steer, speed), or NULL to use buffers.actions. */
+int f110_step(f110_sim *sim, const double *actions_dev, void *stream);
+
+/* Same step with HOST buffers (what a Python/Go/Java caller of the reference API holds):
+ * copies actions in, steps, copies the observation out, and returns when the host buffers are
+ * valid.  obs_block_host: [10][N*A] doubles (see f110_buffers.obs_block) or NULL;
+ * scans_host: [N][A][B] in the handle's scan type or NULL; done_host: [N] bytes or NULL.
+ * Page-locked host buffers give full PCIe rate; pageable ones work. */
+int f110_step_host(f110_sim *sim, const double *actions_host, double *obs_block_host, void *scans_host,
+                   uint8_t *done_host, void *stream);
+
+/* ScanSimulator2D.scan(pose, rng=None) (laser_models.py:429-454) for n poses.
+ * poses_dev: DEVICE [n][3] doubles; out_dev: DEVICE [n][n_beams] in the handle's scan type. */
+int f110_raycast(f110_sim *sim, const double *poses_dev, int32_t n, void *out_dev, void *stream);
+
+int f110_get_buffers(f110_sim *sim, f110_buffers *out);
+int f110_get_config(f110_sim *sim, f110_config *out);
+
+/* Debug/measurement: count EDT lookups with one atomic per warp (adds a little time). */
+int f110_count_lookups(f110_sim *sim, int32_t enable);
+/* Measurement: when enabled, f110_step brackets its ray-cast launch with CUDA events on the caller's
+ * stream; f110_last_raycast_ms waits for that launch and returns its device time in milliseconds. */
+int f110_enable_timing(f110_sim *sim, int32_t enable);
+int f110_last_raycast_ms(f110_sim *sim, float *ms);
+/* Number of kernel launches issued by this handle since creation. */
+int64_t f110_launch_count(f110_sim *sim);
+int f110_synchronize(f110_sim *sim, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* F110_B200_H */

@@ -1,0 +1,115 @@
+"""ctypes binding of libf110_b200.so (include/f110_b200.h).
+
+There is no CPU fallback: if the library is missing, importing this module raises; if there is
+no CUDA device, `f110_create` fails and the wrapper raises RuntimeError.
+"""
+import ctypes
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libf110_b200.so")
+
+F110_ABI_VERSION = 1
+NUM_PARAMS = 18
+PARAM_KEYS = ["mu", "C_Sf", "C_Sr", "lf", "lr", "h", "m", "I", "s_min", "s_max", "sv_min", "sv_max",
+              "v_switch", "a_max", "v_min", "v_max", "width", "length"]
+OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_NOMEM = 0, -1, -2, -3, -4
+INTEGRATOR_RK4, INTEGRATOR_EULER = 1, 2
+PRECISION_FP64, PRECISION_FP32 = 0, 1
+NOISE_OFF, NOISE_TABLE, NOISE_PHILOX = 0, 1, 2
+
+# every symbol include/f110_b200.h declares (tests check the library exports all of them)
+EXPORTS = ["f110_last_error", "f110_abi_version", "f110_device_count", "f110_create", "f110_destroy",
+           "f110_set_map", "f110_set_tables", "f110_set_params", "f110_set_noise_rows", "f110_set_reset_pool",
+           "f110_reset", "f110_step", "f110_step_host", "f110_raycast", "f110_get_buffers", "f110_get_config",
+           "f110_count_lookups", "f110_enable_timing", "f110_last_raycast_ms", "f110_launch_count", "f110_synchronize"]
+
+
+class Config(ctypes.Structure):
+    _fields_ = [("abi_version", ctypes.c_int32), ("n_envs", ctypes.c_int32), ("n_agents", ctypes.c_int32),
+                ("n_beams", ctypes.c_int32), ("integrator", ctypes.c_int32), ("ego_idx", ctypes.c_int32),
+                ("theta_dis", ctypes.c_int32), ("precision", ctypes.c_int32), ("noise_mode", ctypes.c_int32),
+                ("auto_reset", ctypes.c_int32), ("raycast_variant", ctypes.c_int32), ("reserved0", ctypes.c_int32),
+                ("timestep", ctypes.c_double), ("fov", ctypes.c_double), ("eps", ctypes.c_double),
+                ("max_range", ctypes.c_double), ("ttc_thresh", ctypes.c_double), ("noise_std", ctypes.c_double),
+                ("seed", ctypes.c_uint64)]
+
+
+class Buffers(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_void_p) for n in
+                ("state", "obs_block", "collisions", "collision_idx", "lap_times", "lap_counts", "toggles", "done",
+                 "in_collision", "scans", "cur_time", "noise_step", "actions", "episode_count", "lookups")]
+
+
+_lib = None
+
+
+def load():
+    """Load the shared library (raises ImportError with a build hint when it is not there)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "red_gym_b200: %s is missing -- build it with `python red_gym_b200/build.py` "
+            "(needs nvcc, targets sm_100a). There is no CPU fallback." % LIB_PATH)
+    L = ctypes.CDLL(LIB_PATH)
+    vp, i32, i64, f64 = ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64, ctypes.c_double
+    L.f110_last_error.restype = ctypes.c_char_p
+    L.f110_last_error.argtypes = []
+    L.f110_abi_version.restype = ctypes.c_int
+    L.f110_device_count.restype = ctypes.c_int
+    L.f110_create.argtypes = [ctypes.POINTER(Config), ctypes.c_int, ctypes.POINTER(vp)]
+    L.f110_destroy.argtypes = [vp]
+    L.f110_set_map.argtypes = [vp, vp, i32, i32, f64, f64, f64, f64, f64, vp]
+    L.f110_set_tables.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    L.f110_set_params.argtypes = [vp, vp, i32, vp]
+    L.f110_set_noise_rows.argtypes = [vp, vp, i64, i64, vp]
+    L.f110_set_reset_pool.argtypes = [vp, vp, i32, vp]
+    L.f110_reset.argtypes = [vp, vp, vp, vp, vp]
+    L.f110_step.argtypes = [vp, vp, vp]
+    L.f110_step_host.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.f110_raycast.argtypes = [vp, vp, i32, vp, vp]
+    L.f110_get_buffers.argtypes = [vp, ctypes.POINTER(Buffers)]
+    L.f110_get_config.argtypes = [vp, ctypes.POINTER(Config)]
+    L.f110_count_lookups.argtypes = [vp, i32]
+    L.f110_enable_timing.argtypes = [vp, i32]
+    L.f110_last_raycast_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
+    L.f110_launch_count.argtypes = [vp]
+    L.f110_launch_count.restype = i64
+    L.f110_synchronize.argtypes = [vp, vp]
+    for name in EXPORTS:
+        fn = getattr(L, name)
+        if name not in ("f110_last_error", "f110_launch_count"):
+            fn.restype = ctypes.c_int
+    if L.f110_abi_version() != F110_ABI_VERSION:
+        raise ImportError("libf110_b200.so ABI %d != binding %d" % (L.f110_abi_version(), F110_ABI_VERSION))
+    _lib = L
+    return L
+
+
+def last_error():
+    return load().f110_last_error().decode("utf-8", "replace")
+
+
+def check(rc, invalid_exc=ValueError):
+    """Map a status code to the exception the reference raises for the same condition."""
+    if rc == OK:
+        return
+    msg = last_error()
+    if rc == ERR_INVALID:
+        raise invalid_exc(msg)
+    if rc == ERR_STATE:
+        raise ValueError(msg)          # e.g. 'Map is not set for scan simulator.' (laser_models.py:445-446)
+    if rc == ERR_NOMEM:
+        raise MemoryError(msg)
+    raise RuntimeError("libf110_b200: " + msg)
+
+
+class DevArray(object):
+    """Zero-copy view of library-owned device memory for torch.as_tensor (CUDA array interface v2)."""
+
+    def __init__(self, ptr, shape, typestr, owner):
+        self.owner = owner   # keeps the handle alive
+        self.__cuda_array_interface__ = {"shape": tuple(int(s) for s in shape), "typestr": typestr,
+                                         "data": (int(ptr), False), "version": 2, "strides": None}

@@ -1,0 +1,265 @@
+"""BatchF110Env: N independent copies of the reference's F110Env stepped by one GPU.
+
+Same semantics as `F110Env` (f110_env.py:53-416) per env -- same kwargs, same params dict, same
+observation keys -- with a leading env dimension and torch CUDA tensors instead of python lists.
+All arithmetic happens in libf110_b200.so (hand-written sm_100a kernels behind a C ABI); this
+class only owns the handle, uploads setup data and wraps the library's device buffers as
+zero-copy torch tensors.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _native as nat
+from . import host
+
+
+def _integrator_code(integrator):
+    name = integrator if isinstance(integrator, str) else getattr(integrator, "name", None)
+    if name == "RK4":
+        return nat.INTEGRATOR_RK4
+    if name == "Euler":
+        return nat.INTEGRATOR_EULER
+    # base_classes.py:395-396
+    raise SyntaxError("Invalid Integrator Specified. Provided %s. Please choose RK4 or Euler" % (name,))
+
+
+def _hp(a):
+    return a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+
+
+class BatchF110Env(object):
+    """
+    Args (reference kwargs, f110_env.py:100-157): seed, map, map_ext, params, num_agents, timestep,
+        ego_idx, integrator, fov.
+    Batch kwargs: num_envs; device (CUDA ordinal); dtype 'fp64' (parity path) | 'fp32' (fast lidar);
+        noise 'numpy' (host PCG64 rows, parity) | 'philox' (device) | 'off'; num_beams (1080);
+        auto_reset + reset_poses (pool [P, A, 3]) for throughput runs.
+    """
+
+    def __init__(self, num_envs=1, device=0, dtype="fp64", noise=None, num_beams=1080, auto_reset=False,
+                 reset_poses=None, raycast_variant=0, map_data=None, **kwargs):
+        import torch
+        self._torch = torch
+        self.lib = nat.load()
+        self.seed = kwargs.get("seed", 12345)
+        self.map_name = kwargs.get("map", None)
+        self.map_path = host.resolve_map(self.map_name)
+        self.map_ext = kwargs.get("map_ext", ".png")
+        self.params = dict(kwargs.get("params", host.DEFAULT_PARAMS))
+        self.num_agents = kwargs.get("num_agents", 2)
+        self.timestep = kwargs.get("timestep", 0.01)
+        self.ego_idx = kwargs.get("ego_idx", 0)
+        self.integrator = kwargs.get("integrator", "RK4")
+        self.fov = kwargs.get("fov", 2 * np.pi)
+        self.num_envs = int(num_envs)
+        self.num_beams = int(num_beams)
+        self.device_index = int(device)
+        self.dtype = dtype
+        if dtype not in ("fp64", "fp32"):
+            raise ValueError("dtype must be 'fp64' or 'fp32'")
+        if noise is None:
+            noise = "numpy" if dtype == "fp64" else "philox"
+        noise_mode = {"off": nat.NOISE_OFF, "numpy": nat.NOISE_TABLE, "philox": nat.NOISE_PHILOX}[noise]
+        self.noise = noise
+        cfg = nat.Config(abi_version=nat.F110_ABI_VERSION, n_envs=self.num_envs, n_agents=self.num_agents,
+                         n_beams=self.num_beams, integrator=_integrator_code(self.integrator), ego_idx=self.ego_idx,
+                         theta_dis=2000, precision=nat.PRECISION_FP64 if dtype == "fp64" else nat.PRECISION_FP32,
+                         noise_mode=noise_mode, auto_reset=1 if auto_reset else 0, raycast_variant=raycast_variant,
+                         timestep=self.timestep, fov=self.fov, eps=1e-4, max_range=30.0, ttc_thresh=0.005,
+                         noise_std=0.01, seed=self.seed)
+        h = ctypes.c_void_p()
+        nat.check(self.lib.f110_create(ctypes.byref(cfg), self.device_index, ctypes.byref(h)))
+        self._h = h
+        self.device = torch.device("cuda", self.device_index)
+        self._noise_rows = 0
+        self._steps_since_full_reset = 0
+        # setup uploads
+        sines, cosines = host.trig_tables(2000)
+        self.scan_angles, beam_cos, side = host.beam_tables(self.num_beams, self.fov, self.params)
+        nat.check(self.lib.f110_set_tables(h, _hp(sines), _hp(cosines), _hp(self.scan_angles), _hp(beam_cos), _hp(side), None))
+        pv = host.params_vector(self.params)
+        nat.check(self.lib.f110_set_params(h, _hp(pv), -1, None))
+        nat.check(self.lib.f110_set_params(h, _hp(pv), self.num_agents, None))
+        self.map = None
+        if map_data is not None:
+            self._upload_map(map_data)
+        else:
+            self._upload_map(host.MapData(self.map_path, self.map_ext))
+        if self.noise == "numpy":
+            self._ensure_noise(64)
+        if reset_poses is not None:
+            self.set_reset_pool(reset_poses)
+        self._wrap_buffers()
+
+    # ------------------------------------------------------------------ setup
+    def _stream(self):
+        return ctypes.c_void_p(self._torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _upload_map(self, m):
+        self.map = m
+        nat.check(self.lib.f110_set_map(self._h, _hp(m.edt), m.height, m.width, m.resolution, m.origin[0], m.origin[1],
+                                        m.orig_c, m.orig_s, None))
+
+    def _ensure_noise(self, rows):
+        if self.noise != "numpy" or rows <= self._noise_rows:
+            return
+        target = max(64, self._noise_rows)
+        while target < rows:
+            target *= 2
+        new = host.noise_rows(self.seed, self._noise_rows, target - self._noise_rows, self.num_beams)
+        nat.check(self.lib.f110_set_noise_rows(self._h, _hp(np.ascontiguousarray(new)), self._noise_rows, new.shape[0], None))
+        self._noise_rows = target
+
+    def _wrap_buffers(self):
+        torch = self._torch
+        b = nat.Buffers()
+        nat.check(self.lib.f110_get_buffers(self._h, ctypes.byref(b)))
+        N, A, B = self.num_envs, self.num_agents, self.num_beams
+
+        def t(ptr, shape, typestr):
+            return torch.as_tensor(nat.DevArray(ptr, shape, typestr, self), device=self.device)
+
+        self.state = t(b.state, (7, N, A), "<f8")
+        self.obs_block = t(b.obs_block, (10, N, A), "<f8")
+        self.collisions = t(b.collisions, (N, A), "<f8")
+        self.collision_idx = t(b.collision_idx, (N, A), "<f8")
+        self.lap_times = t(b.lap_times, (N, A), "<f8")
+        self.lap_counts = t(b.lap_counts, (N, A), "<f8")
+        self.toggle_list = t(b.toggles, (N, A), "<i4")
+        self.done = t(b.done, (N,), "|u1")
+        self.in_collision = t(b.in_collision, (N, A), "|u1")
+        self.scans = t(b.scans, (N, A, B), "<f8" if self.dtype == "fp64" else "<f4")
+        self.current_time = t(b.cur_time, (N,), "<f8")
+        self.noise_step = t(b.noise_step, (N,), "<i8")
+        self.actions = t(b.actions, (N, A, 2), "<f8")
+        self.episode_count = t(b.episode_count, (N,), "<i8")
+        self._lookups = t(b.lookups, (1,), "<i8")
+        self._zeros_na = torch.zeros((N, A), dtype=torch.float64, device=self.device)
+
+    def set_reset_pool(self, poses):
+        poses = np.ascontiguousarray(np.asarray(poses, dtype=np.float64).reshape(-1, self.num_agents, 3))
+        nat.check(self.lib.f110_set_reset_pool(self._h, _hp(poses), poses.shape[0], None))
+
+    # ------------------------------------------------------------------ reference API (batched)
+    def update_map(self, map_path, map_ext):
+        """F110Env.update_map (f110_env.py:349-360): map_path is the yaml path."""
+        self._upload_map(host.MapData(map_path, map_ext))
+
+    def update_params(self, params, index=-1):
+        """F110Env.update_params -> Simulator.update_params (f110_env.py:362, base_classes.py:507-527)."""
+        if index >= self.num_agents:
+            raise IndexError("Index given is out of bounds for list of agents.")
+        pv = host.params_vector(params)
+        nat.check(self.lib.f110_set_params(self._h, _hp(pv), -1 if index < 0 else index, None), IndexError)
+
+    def reset(self, poses, mask=None):
+        """F110Env.reset (f110_env.py:304-347).  poses: (N, A, 3) [x, y, yaw] host array/tensor.
+        mask: optional (N,) bool -- only those envs are reset (the others are untouched)."""
+        poses = np.asarray(poses.cpu() if hasattr(poses, "cpu") else poses, dtype=np.float64)
+        if poses.ndim == 2 and self.num_envs == 1:
+            poses = poses[None]
+        if poses.shape[0] != self.num_envs:
+            raise ValueError("Number of pose sets for reset does not match number of envs.")
+        if poses.shape[1] != self.num_agents:
+            raise ValueError("Number of poses for reset does not match number of agents.")   # base_classes.py:618-619
+        poses = np.ascontiguousarray(poses)
+        rot = host.start_rotation(poses[:, self.ego_idx, 2])
+        m = None
+        if mask is not None:
+            m = np.ascontiguousarray(np.asarray(mask.cpu() if hasattr(mask, "cpu") else mask).astype(np.uint8))
+        else:
+            self._steps_since_full_reset = 0
+        self._ensure_noise(2)
+        nat.check(self.lib.f110_reset(self._h, _hp(poses), _hp(rot), _hp(m), self._stream()))
+        self._steps_since_full_reset += 1
+        return self._obs()
+
+    def step(self, action):
+        """F110Env.step (f110_env.py:261-302).  action: (N, A, 2) [steer, speed]; a CUDA float64 tensor is used
+        in place, anything else is copied to the device first."""
+        torch = self._torch
+        if not isinstance(action, torch.Tensor):
+            action = torch.from_numpy(np.ascontiguousarray(np.asarray(action, dtype=np.float64)))
+        if action.numel() != self.num_envs * self.num_agents * 2:
+            raise ValueError("action must have shape (num_envs, num_agents, 2)")
+        if action.is_cuda and action.dtype == torch.float64 and action.is_contiguous():
+            ptr = ctypes.c_void_p(action.data_ptr())
+        else:
+            self.actions.copy_(action.reshape(self.num_envs, self.num_agents, 2), non_blocking=True)
+            ptr = None
+        self._steps_since_full_reset += 1
+        self._ensure_noise(self._steps_since_full_reset + 1)
+        nat.check(self.lib.f110_step(self._h, ptr, self._stream()))
+        return self._obs()
+
+    def _obs(self):
+        s = self.state
+        obs = {"ego_idx": self.ego_idx, "scans": self.scans, "poses_x": s[0], "poses_y": s[1], "poses_theta": s[4],
+               "linear_vels_x": s[3], "linear_vels_y": self._zeros_na, "ang_vels_z": s[5],
+               "collisions": self.collisions, "lap_times": self.lap_times, "lap_counts": self.lap_counts}
+        reward = self.timestep
+        info = {"checkpoint_done": self.toggle_list >= 4}
+        return obs, reward, self.done.bool(), info
+
+    def step_host(self, actions, obs_block_out, scans_out=None, done_out=None):
+        """One step through f110_step_host: host actions in, host observation out (pinned numpy/torch buffers)."""
+        def ptr(x):
+            if x is None:
+                return None
+            return ctypes.c_void_p(x.data_ptr()) if hasattr(x, "data_ptr") else _hp(x)
+        self._steps_since_full_reset += 1
+        self._ensure_noise(self._steps_since_full_reset + 1)
+        nat.check(self.lib.f110_step_host(self._h, ptr(actions), ptr(obs_block_out), ptr(scans_out), ptr(done_out), self._stream()))
+
+    def render(self, mode="human"):
+        """The reference renders through pyglet/OpenGL (f110_env.py:385-416): unavailable on this box."""
+        assert mode in ["human", "human_fast"]
+
+    # ------------------------------------------------------------------ extras
+    def raycast(self, poses, out=None):
+        """ScanSimulator2D.scan(pose, None) for a batch of poses (n, 3) -> (n, num_beams)."""
+        torch = self._torch
+        poses = torch.as_tensor(poses, dtype=torch.float64, device=self.device).contiguous()
+        n = poses.shape[0]
+        if out is None:
+            out = torch.empty((n, self.num_beams), dtype=torch.float64 if self.dtype == "fp64" else torch.float32, device=self.device)
+        nat.check(self.lib.f110_raycast(self._h, ctypes.c_void_p(poses.data_ptr()), n, ctypes.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+    def count_lookups(self, enable=True):
+        nat.check(self.lib.f110_count_lookups(self._h, 1 if enable else 0))
+        self._lookups.zero_()
+
+    def lookups(self, clear=True):
+        v = int(self._lookups.item())
+        if clear:
+            self._lookups.zero_()
+        return v
+
+    def enable_timing(self, enable=True):
+        nat.check(self.lib.f110_enable_timing(self._h, 1 if enable else 0))
+
+    def last_raycast_ms(self):
+        ms = ctypes.c_float()
+        nat.check(self.lib.f110_last_raycast_ms(self._h, ctypes.byref(ms)))
+        return float(ms.value)
+
+    @property
+    def launch_count(self):
+        return int(self.lib.f110_launch_count(self._h))
+
+    def synchronize(self):
+        self._torch.cuda.synchronize(self.device)
+
+    def close(self):
+        h = getattr(self, "_h", None)
+        if h:
+            self.lib.f110_destroy(h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,503 @@
+// C ABI of libf110_b200.so (see include/f110_b200.h).  Owns device memory, stages host data,
+// orders the kernels of one step on the caller's stream.  No CPU fallback anywhere.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/f110_b200.h"
+#include "f110_dev.h"
+
+static thread_local std::string g_err;
+static int fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return fail(F110_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+struct f110_sim {
+    f110_config cfg;
+    int device;
+    F110Dev d;
+    std::vector<void *> allocs;
+    bool has_map = false, has_tables = false;
+    double *edt64 = nullptr, *edt64_t = nullptr;
+    float *edt32_t = nullptr;
+    float2 *dir32 = nullptr;
+    double *noise = nullptr;
+    long long noise_cap = 0;
+    double *pool = nullptr;
+    double *obs_block = nullptr;
+    double *actions = nullptr;
+    double *stage_poses = nullptr, *stage_rot = nullptr;
+    uint8_t *stage_mask = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+    std::vector<cudaEvent_t> chunk_ev;
+    long long launches = 0;
+    bool timing = false;
+};
+
+template <typename T>
+static int dev_alloc(f110_sim *s, T **p, size_t n, bool zero = true)
+{
+    void *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, n * sizeof(T) > 0 ? n * sizeof(T) : 16);
+    if (e != cudaSuccess) return fail(F110_ERR_NOMEM, "cudaMalloc(%zu bytes) failed: %s", n * sizeof(T), cudaGetErrorString(e));
+    if (zero) cudaMemset(q, 0, n * sizeof(T));
+    s->allocs.push_back(q);
+    *p = (T *)q;
+    return 0;
+}
+#define TRY(x) do { int r_ = (x); if (r_) return r_; } while (0)
+
+extern "C" const char *f110_last_error(void) { return g_err.c_str(); }
+extern "C" int f110_abi_version(void) { return F110_ABI_VERSION; }
+extern "C" int f110_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
+{
+    if (!cfg || !out) return fail(F110_ERR_INVALID, "null argument");
+    if (cfg->abi_version != F110_ABI_VERSION) return fail(F110_ERR_INVALID, "abi_version %d != %d", cfg->abi_version, F110_ABI_VERSION);
+    if (cfg->n_envs < 1 || cfg->n_agents < 1 || cfg->n_agents > F110_MAX_AGENTS || cfg->n_beams < 2 || cfg->theta_dis < 1)
+        return fail(F110_ERR_INVALID, "bad sizes: n_envs=%d n_agents=%d n_beams=%d", cfg->n_envs, cfg->n_agents, cfg->n_beams);
+    if (cfg->integrator != F110_INTEGRATOR_RK4 && cfg->integrator != F110_INTEGRATOR_EULER)
+        return fail(F110_ERR_INVALID, "Invalid Integrator Specified (%d)", cfg->integrator);
+    if (cfg->ego_idx < 0 || cfg->ego_idx >= cfg->n_agents) return fail(F110_ERR_INVALID, "ego_idx out of range");
+    if (cfg->precision == F110_PRECISION_FP32 && cfg->noise_mode == F110_NOISE_TABLE)
+        return fail(F110_ERR_INVALID, "the fp32 path takes F110_NOISE_OFF or F110_NOISE_PHILOX");
+    if (cfg->precision == F110_PRECISION_FP64 && cfg->noise_mode == F110_NOISE_PHILOX)
+        return fail(F110_ERR_INVALID, "the fp64 path takes F110_NOISE_OFF or F110_NOISE_TABLE");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(F110_ERR_CUDA, "no CUDA device available (%s); this library has no CPU path", e != cudaSuccess ? cudaGetErrorString(e) : "0 devices");
+    }
+    if (device < 0 || device >= ndev) return fail(F110_ERR_INVALID, "device %d out of range (%d devices)", device, ndev);
+    CK(cudaSetDevice(device));
+    f110_sim *s = new f110_sim();
+    s->cfg = *cfg;
+    s->device = device;
+    F110Dev &d = s->d;
+    memset(&d, 0, sizeof(d));
+    const size_t N = cfg->n_envs, A = cfg->n_agents, NA = N * A, B = cfg->n_beams;
+    d.n_envs = cfg->n_envs; d.n_agents = cfg->n_agents; d.n_beams = cfg->n_beams; d.integrator = cfg->integrator;
+    d.ego_idx = cfg->ego_idx; d.theta_dis = cfg->theta_dis; d.noise_mode = cfg->noise_mode; d.auto_reset = cfg->auto_reset;
+    d.scan_is_f32 = cfg->precision == F110_PRECISION_FP32;
+    d.timestep = cfg->timestep; d.fov = cfg->fov; d.eps = cfg->eps; d.max_range = cfg->max_range;
+    d.ttc_thresh = cfg->ttc_thresh; d.noise_std = cfg->noise_std; d.seed = cfg->seed;
+    // laser_models.py:367-368
+    double angle_increment = cfg->fov / (cfg->n_beams - 1);
+    d.theta_inc = cfg->theta_dis * angle_increment / (2. * M_PI);
+    int rc = 0;
+    do {
+        // obs block: 7 state fields + collisions + lap_times + lap_counts, contiguous for a single D2H copy
+        if ((rc = dev_alloc(s, &s->obs_block, 10 * NA))) break;
+        d.state = s->obs_block;
+        d.collisions = s->obs_block + 7 * NA;
+        d.lap_times = s->obs_block + 8 * NA;
+        d.lap_counts = s->obs_block + 9 * NA;
+        if ((rc = dev_alloc(s, &d.pose_pre, 3 * NA))) break;
+        if ((rc = dev_alloc(s, &d.steer_buf, 2 * NA))) break;
+        if ((rc = dev_alloc(s, &d.steer_len, NA))) break;
+        if ((rc = dev_alloc(s, &d.in_collision, NA))) break;
+        if ((rc = dev_alloc(s, &d.collision_idx, NA))) break;
+        if ((rc = dev_alloc(s, &d.toggles, NA))) break;
+        if ((rc = dev_alloc(s, &d.near_start, NA))) break;
+        if ((rc = dev_alloc(s, &d.start_x, NA))) break;
+        if ((rc = dev_alloc(s, &d.start_y, NA))) break;
+        if ((rc = dev_alloc(s, &d.start_rot, 4 * N))) break;
+        if ((rc = dev_alloc(s, &d.cur_time, N))) break;
+        if ((rc = dev_alloc(s, &d.noise_step, N))) break;
+        if ((rc = dev_alloc(s, &d.done, N))) break;
+        if ((rc = dev_alloc(s, &d.reset_pending, N))) break;
+        if ((rc = dev_alloc(s, &d.episode_count, N))) break;
+        if ((rc = dev_alloc(s, &s->actions, 2 * NA))) break;
+        if ((rc = dev_alloc(s, &d.lookups, 1))) break;
+        if ((rc = dev_alloc(s, &s->stage_poses, 3 * NA))) break;
+        if ((rc = dev_alloc(s, &s->stage_rot, 4 * N))) break;
+        if ((rc = dev_alloc(s, &s->stage_mask, N))) break;
+        size_t scan_bytes = NA * B * (d.scan_is_f32 ? 4 : 8);
+        uint8_t *scans = nullptr;
+        if ((rc = dev_alloc(s, &scans, scan_bytes, false))) break;
+        d.scans = scans;
+        double *tabs = nullptr;
+        if ((rc = dev_alloc(s, &tabs, 2 * (size_t)cfg->theta_dis + 3 * B))) break;
+        d.sines = tabs; d.cosines = tabs + cfg->theta_dis;
+        d.scan_angles = tabs + 2 * cfg->theta_dis; d.beam_cos = d.scan_angles + B; d.side_dist = d.beam_cos + B;
+        float *tabs32 = nullptr;
+        if ((rc = dev_alloc(s, &tabs32, 2 * B))) break;
+        d.beam_cos32 = tabs32; d.side_dist32 = tabs32 + B;
+        if ((rc = dev_alloc(s, &s->dir32, (size_t)cfg->theta_dis))) break;
+        d.dir32 = s->dir32;
+        double *params = nullptr;
+        if ((rc = dev_alloc(s, &params, (A + 1) * F110_NP))) break;
+        d.params = params;
+    } while (0);
+    if (rc) { f110_destroy(s); return rc; }
+    // start_rot = identity, collision_idx = -1, near_start = 1 (f110_env.py:182-187, base_classes.py:481)
+    {
+        std::vector<double> rot(4 * N, 0.0), ci(NA, -1.0);
+        for (size_t e2 = 0; e2 < N; e2++) { rot[4 * e2] = 1.0; rot[4 * e2 + 3] = 1.0; }
+        cudaMemcpy(d.start_rot, rot.data(), rot.size() * 8, cudaMemcpyHostToDevice);
+        cudaMemcpy(d.collision_idx, ci.data(), ci.size() * 8, cudaMemcpyHostToDevice);
+        cudaMemset(d.near_start, 1, NA);
+    }
+    d.actions = s->actions;
+    cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking);
+    cudaEventCreate(&s->ev_a);
+    cudaEventCreate(&s->ev_b);
+    e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { f110_destroy(s); return fail(F110_ERR_CUDA, "init failed: %s", cudaGetErrorString(e)); }
+    *out = s;
+    return F110_OK;
+}
+
+extern "C" int f110_destroy(f110_sim *s)
+{
+    if (!s) return F110_OK;
+    cudaSetDevice(s->device);
+    cudaDeviceSynchronize();
+    for (void *p : s->allocs) cudaFree(p);
+    if (s->edt64) cudaFree(s->edt64);
+    if (s->edt64_t) cudaFree(s->edt64_t);
+    if (s->edt32_t) cudaFree(s->edt32_t);
+    if (s->noise) cudaFree(s->noise);
+    if (s->pool) cudaFree(s->pool);
+    for (cudaEvent_t ev : s->chunk_ev) cudaEventDestroy(ev);
+    if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+    if (s->ev_a) cudaEventDestroy(s->ev_a);
+    if (s->ev_b) cudaEventDestroy(s->ev_b);
+    delete s;
+    return F110_OK;
+}
+
+extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w, double res, double ox, double oy,
+                            double oc, double os, void *stream)
+{
+    if (!s || !edt || h < 1 || w < 1 || !(res > 0)) return fail(F110_ERR_INVALID, "bad map arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(cudaSetDevice(s->device));
+    CK(cudaStreamSynchronize(st));
+    if (s->edt64) { cudaFree(s->edt64); cudaFree(s->edt64_t); cudaFree(s->edt32_t); s->edt64 = nullptr; }
+    F110Dev &d = s->d;
+    size_t cells = (size_t)h * w;
+    int tx64 = (w + F110_T64_W - 1) / F110_T64_W, ty64 = (h + F110_T64_H - 1) / F110_T64_H;
+    int tx32 = (w + F110_T32_W - 1) / F110_T32_W, ty32 = (h + F110_T32_H - 1) / F110_T32_H;
+    CK(cudaMalloc(&s->edt64, cells * 8));
+    CK(cudaMalloc(&s->edt64_t, (size_t)tx64 * ty64 * 16 * 8));
+    CK(cudaMalloc(&s->edt32_t, (size_t)tx32 * ty32 * 32 * 4));
+    CK(cudaMemcpyAsync(s->edt64, edt, cells * 8, cudaMemcpyHostToDevice, st));
+    d.map_h = h; d.map_w = w; d.res = res; d.inv_res = 1.0 / res; d.ox = ox; d.oy = oy; d.oc = oc; d.os = os;
+    d.xmax = w * res; d.ymax = h * res;   // width * resolution, height * resolution (laser_models.py:79)
+    int ex;
+    d.res_pow2 = (frexp(res, &ex) == 0.5);
+    d.has_rot = !(oc == 1.0 && os == 0.0);
+    d.tiles_x64 = tx64; d.tiles_x32 = tx32;
+    d.oob64 = edt[cells - 1];             // dt[-1, -1]
+    d.oob32 = (float)(edt[cells - 1] / res);
+    d.edt64 = s->edt64; d.edt64_t = s->edt64_t; d.edt32_t = s->edt32_t;
+    f110_launch_tile64(s->edt64, s->edt64_t, h, w, st);
+    f110_launch_tile32(s->edt64, s->edt32_t, h, w, d.inv_res, st);
+    s->launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));
+    s->has_map = true;
+    // direction table depends on the map rotation: rebuild if tables are already there
+    if (s->has_tables) {
+        std::vector<double> sn(d.theta_dis), cs(d.theta_dis);
+        CK(cudaMemcpy(sn.data(), d.sines, d.theta_dis * 8, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(cs.data(), d.cosines, d.theta_dis * 8, cudaMemcpyDeviceToHost));
+        std::vector<float2> dir(d.theta_dis);
+        for (int i = 0; i < d.theta_dis; i++)
+            dir[i] = make_float2((float)(cs[i] * oc + sn[i] * os), (float)(-cs[i] * os + sn[i] * oc));
+        CK(cudaMemcpy(s->dir32, dir.data(), dir.size() * sizeof(float2), cudaMemcpyHostToDevice));
+    }
+    return F110_OK;
+}
+
+extern "C" int f110_set_tables(f110_sim *s, const double *sines, const double *cosines, const double *scan_angles,
+                               const double *beam_cosines, const double *side_distances, void *stream)
+{
+    if (!s || !sines || !cosines || !scan_angles || !beam_cosines || !side_distances) return fail(F110_ERR_INVALID, "null table");
+    CK(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(cudaStreamSynchronize(st));
+    F110Dev &d = s->d;
+    const int T = d.theta_dis, B = d.n_beams;
+    CK(cudaMemcpy((void *)d.sines, sines, T * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy((void *)d.cosines, cosines, T * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy((void *)d.scan_angles, scan_angles, B * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy((void *)d.beam_cos, beam_cosines, B * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy((void *)d.side_dist, side_distances, B * 8, cudaMemcpyHostToDevice));
+    std::vector<float> f(2 * B);
+    for (int i = 0; i < B; i++) { f[i] = (float)beam_cosines[i]; f[B + i] = (float)side_distances[i]; }
+    CK(cudaMemcpy((void *)d.beam_cos32, f.data(), f.size() * 4, cudaMemcpyHostToDevice));
+    double oc = s->has_map ? d.oc : 1.0, os = s->has_map ? d.os : 0.0;
+    std::vector<float2> dir(T);
+    for (int i = 0; i < T; i++)
+        dir[i] = make_float2((float)(cosines[i] * oc + sines[i] * os), (float)(-cosines[i] * os + sines[i] * oc));
+    CK(cudaMemcpy(s->dir32, dir.data(), dir.size() * sizeof(float2), cudaMemcpyHostToDevice));
+    s->has_tables = true;
+    return F110_OK;
+}
+
+extern "C" int f110_set_params(f110_sim *s, const double *p, int32_t agent_idx, void *stream)
+{
+    if (!s || !p) return fail(F110_ERR_INVALID, "null argument");
+    CK(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int A = s->d.n_agents;
+    if (agent_idx > A) return fail(F110_ERR_INVALID, "Index given is out of bounds for list of agents.");
+    CK(cudaStreamSynchronize(st));
+    double *base = (double *)s->d.params;
+    if (agent_idx == A) {
+        double wl[2] = { p[F110_P_WIDTH], p[F110_P_LENGTH] };
+        CK(cudaMemcpy(base + (size_t)F110_NP * A, wl, 16, cudaMemcpyHostToDevice));
+    } else if (agent_idx < 0) {
+        for (int a = 0; a < A; a++) CK(cudaMemcpy(base + (size_t)F110_NP * a, p, F110_NP * 8, cudaMemcpyHostToDevice));
+    } else {
+        CK(cudaMemcpy(base + (size_t)F110_NP * agent_idx, p, F110_NP * 8, cudaMemcpyHostToDevice));
+    }
+    return F110_OK;
+}
+
+extern "C" int f110_set_noise_rows(f110_sim *s, const double *rows, int64_t first_row, int64_t n_rows, void *stream)
+{
+    if (!s || !rows || first_row < 0 || n_rows < 1) return fail(F110_ERR_INVALID, "bad noise rows");
+    if (s->cfg.noise_mode != F110_NOISE_TABLE) return fail(F110_ERR_STATE, "handle was not created with F110_NOISE_TABLE");
+    CK(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t B = s->d.n_beams;
+    long long need = first_row + n_rows;
+    if (need > s->noise_cap) {
+        long long cap = s->noise_cap ? s->noise_cap : 256;
+        while (cap < need) cap *= 2;
+        double *nn = nullptr;
+        CK(cudaStreamSynchronize(st));
+        CK(cudaMalloc(&nn, (size_t)cap * B * 8));
+        if (s->noise) {
+            CK(cudaMemcpy(nn, s->noise, (size_t)s->d.noise_rows * B * 8, cudaMemcpyDeviceToDevice));
+            cudaFree(s->noise);
+        }
+        s->noise = nn; s->noise_cap = cap;
+        s->d.noise = nn;
+    }
+    CK(cudaMemcpyAsync(s->noise + (size_t)first_row * B, rows, (size_t)n_rows * B * 8, cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    if (need > s->d.noise_rows) s->d.noise_rows = need;
+    return F110_OK;
+}
+
+extern "C" int f110_set_reset_pool(f110_sim *s, const double *poses, int32_t n_poses, void *stream)
+{
+    if (!s || !poses || n_poses < 1) return fail(F110_ERR_INVALID, "bad reset pool");
+    CK(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(cudaStreamSynchronize(st));
+    if (s->pool) cudaFree(s->pool);
+    size_t n = (size_t)n_poses * s->d.n_agents * 3;
+    CK(cudaMalloc(&s->pool, n * 8));
+    CK(cudaMemcpy(s->pool, poses, n * 8, cudaMemcpyHostToDevice));
+    s->d.pool = s->pool; s->d.n_pool = n_poses;
+    return F110_OK;
+}
+
+static int check_ready(f110_sim *s)
+{
+    if (!s) return fail(F110_ERR_INVALID, "null handle");
+    if (!s->has_map) return fail(F110_ERR_STATE, "Map is not set for scan simulator.");
+    if (!s->has_tables) return fail(F110_ERR_STATE, "scan tables are not set");
+    if (s->cfg.noise_mode == F110_NOISE_TABLE && s->d.noise_rows < 1) return fail(F110_ERR_STATE, "noise rows are not set");
+    if (s->cfg.auto_reset && s->d.n_pool < 1) return fail(F110_ERR_STATE, "auto_reset needs f110_set_reset_pool");
+    return 0;
+}
+
+// kernels of one step, in the order of Simulator.step + F110Env.step
+static int enqueue_step(f110_sim *s, const uint8_t *mask_dev, cudaStream_t st)
+{
+    F110Dev &d = s->d;
+    d.step_mask = mask_dev;
+    f110_launch_dynamics(d, st);
+    if (s->timing) cudaEventRecord(s->ev_a, st);
+    if (d.scan_is_f32) f110_launch_raycast32(d, 0, d.n_envs, s->cfg.raycast_variant, st);
+    else f110_launch_raycast64(d, 0, d.n_envs, s->cfg.raycast_variant, st);
+    if (s->timing) cudaEventRecord(s->ev_b, st);
+    s->launches += 2;
+    if (d.n_agents > 1) { f110_launch_agents(d, st); s->launches++; }
+    f110_launch_finalize(d, st);
+    s->launches++;
+    d.step_mask = nullptr;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int f110_reset(f110_sim *s, const double *poses, const double *start_rot, const uint8_t *mask, void *stream)
+{
+    TRY(check_ready(s));
+    if (!poses) return fail(F110_ERR_INVALID, "Number of poses for reset does not match number of agents.");
+    CK(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t N = s->d.n_envs, NA = N * s->d.n_agents;
+    CK(cudaMemcpyAsync(s->stage_poses, poses, 3 * NA * 8, cudaMemcpyHostToDevice, st));
+    if (start_rot) CK(cudaMemcpyAsync(s->stage_rot, start_rot, 4 * N * 8, cudaMemcpyHostToDevice, st));
+    if (mask) CK(cudaMemcpyAsync(s->stage_mask, mask, N, cudaMemcpyHostToDevice, st));
+    f110_launch_reset(s->d, s->stage_poses, start_rot ? s->stage_rot : nullptr, mask ? s->stage_mask : nullptr, st);
+    s->launches++;
+    // zero-action step (f110_env.py:335-336) on the reset envs only
+    const double *saved = s->d.actions;
+    double *zero = s->stage_poses;   // reuse: k_reset has consumed it by the time the memset runs (stream order)
+    CK(cudaMemsetAsync(zero, 0, 2 * NA * 8, st));
+    s->d.actions = zero;
+    int rc = enqueue_step(s, mask ? s->stage_mask : nullptr, st);
+    s->d.actions = saved;
+    if (rc) return rc;
+    // the staging buffers are reused by the next call
+    CK(cudaStreamSynchronize(st));
+    return F110_OK;
+}
+
+extern "C" int f110_step(f110_sim *s, const double *actions_dev, void *stream)
+{
+    TRY(check_ready(s));
+    CK(cudaSetDevice(s->device));
+    s->d.actions = actions_dev ? actions_dev : s->actions;
+    int rc = enqueue_step(s, nullptr, (cudaStream_t)stream);
+    s->d.actions = s->actions;
+    return rc;
+}
+
+extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *obs_block_host, void *scans_host,
+                              uint8_t *done_host, void *stream)
+{
+    TRY(check_ready(s));
+    if (!actions_host) return fail(F110_ERR_INVALID, "null actions");
+    CK(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    F110Dev &d = s->d;
+    const size_t N = d.n_envs, A = d.n_agents, NA = N * A, B = d.n_beams;
+    const size_t esz = d.scan_is_f32 ? 4 : 8;
+    CK(cudaMemcpyAsync(s->actions, actions_host, 2 * NA * 8, cudaMemcpyHostToDevice, st));
+    d.actions = s->actions;
+    d.step_mask = nullptr;
+    f110_launch_dynamics(d, st);
+    s->launches++;
+    // The scans dominate the D2H traffic.  With one agent per env nothing after the ray-cast touches
+    // them, so the ray-cast is issued in env chunks and each chunk's copy-out (on a second stream)
+    // overlaps the next chunk's kernel.
+    int chunks = 1;
+    if (scans_host && A == 1 && N >= 8192) chunks = 8;
+    if ((int)s->chunk_ev.size() < chunks) {
+        size_t old = s->chunk_ev.size();
+        s->chunk_ev.resize(chunks);
+        for (size_t i = old; i < s->chunk_ev.size(); i++) cudaEventCreateWithFlags(&s->chunk_ev[i], cudaEventDisableTiming);
+    }
+    size_t per = (N + chunks - 1) / chunks;
+    for (int c = 0; c < chunks; c++) {
+        size_t b = c * per, cnt = (b + per <= N) ? per : (N > b ? N - b : 0);
+        if (!cnt) break;
+        if (d.scan_is_f32) f110_launch_raycast32(d, (int)b, (int)cnt, s->cfg.raycast_variant, st);
+        else f110_launch_raycast64(d, (int)b, (int)cnt, s->cfg.raycast_variant, st);
+        s->launches++;
+        if (chunks > 1) {
+            CK(cudaEventRecord(s->chunk_ev[c], st));
+            CK(cudaStreamWaitEvent(s->copy_stream, s->chunk_ev[c], 0));
+            CK(cudaMemcpyAsync((char *)scans_host + b * A * B * esz, (char *)d.scans + b * A * B * esz, cnt * A * B * esz,
+                               cudaMemcpyDeviceToHost, s->copy_stream));
+        }
+    }
+    if (A > 1) { f110_launch_agents(d, st); s->launches++; }
+    f110_launch_finalize(d, st);
+    s->launches++;
+    CK(cudaGetLastError());
+    if (scans_host && chunks == 1)
+        CK(cudaMemcpyAsync(scans_host, d.scans, NA * B * esz, cudaMemcpyDeviceToHost, st));
+    if (obs_block_host) CK(cudaMemcpyAsync(obs_block_host, s->obs_block, 10 * NA * 8, cudaMemcpyDeviceToHost, st));
+    if (done_host) CK(cudaMemcpyAsync(done_host, d.done, N, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (chunks > 1) CK(cudaStreamSynchronize(s->copy_stream));
+    return F110_OK;
+}
+
+extern "C" int f110_raycast(f110_sim *s, const double *poses_dev, int32_t n, void *out_dev, void *stream)
+{
+    if (!s) return fail(F110_ERR_INVALID, "null handle");
+    if (!s->has_map) return fail(F110_ERR_STATE, "Map is not set for scan simulator.");
+    if (!s->has_tables) return fail(F110_ERR_STATE, "scan tables are not set");
+    if (!poses_dev || !out_dev || n < 0) return fail(F110_ERR_INVALID, "bad raycast arguments");
+    CK(cudaSetDevice(s->device));
+    if (s->d.scan_is_f32) f110_launch_scan_only32(s->d, poses_dev, n, (float *)out_dev, s->cfg.raycast_variant, (cudaStream_t)stream);
+    else f110_launch_scan_only64(s->d, poses_dev, n, (double *)out_dev, s->cfg.raycast_variant, (cudaStream_t)stream);
+    s->launches++;
+    CK(cudaGetLastError());
+    return F110_OK;
+}
+
+extern "C" int f110_get_buffers(f110_sim *s, f110_buffers *o)
+{
+    if (!s || !o) return fail(F110_ERR_INVALID, "null argument");
+    F110Dev &d = s->d;
+    o->state = d.state; o->obs_block = s->obs_block; o->collisions = d.collisions; o->collision_idx = d.collision_idx;
+    o->lap_times = d.lap_times; o->lap_counts = d.lap_counts; o->toggles = d.toggles; o->done = d.done;
+    o->in_collision = d.in_collision; o->scans = d.scans; o->cur_time = d.cur_time; o->noise_step = (int64_t *)d.noise_step;
+    o->actions = s->actions; o->episode_count = (int64_t *)d.episode_count; o->lookups = (uint64_t *)d.lookups;
+    return F110_OK;
+}
+
+extern "C" int f110_get_config(f110_sim *s, f110_config *o)
+{
+    if (!s || !o) return fail(F110_ERR_INVALID, "null argument");
+    *o = s->cfg;
+    return F110_OK;
+}
+
+extern "C" int f110_count_lookups(f110_sim *s, int32_t enable)
+{
+    if (!s) return fail(F110_ERR_INVALID, "null handle");
+    s->d.count_lookups = enable ? 1 : 0;
+    return F110_OK;
+}
+
+extern "C" int f110_enable_timing(f110_sim *s, int32_t enable)
+{
+    if (!s) return fail(F110_ERR_INVALID, "null handle");
+    s->timing = enable != 0;
+    return F110_OK;
+}
+
+extern "C" int f110_last_raycast_ms(f110_sim *s, float *ms)
+{
+    if (!s || !ms) return fail(F110_ERR_INVALID, "null argument");
+    CK(cudaSetDevice(s->device));
+    CK(cudaEventSynchronize(s->ev_b));
+    CK(cudaEventElapsedTime(ms, s->ev_a, s->ev_b));
+    return F110_OK;
+}
+
+extern "C" int64_t f110_launch_count(f110_sim *s) { return s ? s->launches : 0; }
+
+extern "C" int f110_synchronize(f110_sim *s, void *stream)
+{
+    if (!s) return fail(F110_ERR_INVALID, "null handle");
+    CK(cudaSetDevice(s->device));
+    CK(cudaStreamSynchronize((cudaStream_t)stream));
+    return F110_OK;
+}

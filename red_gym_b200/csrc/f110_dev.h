@@ -1,0 +1,74 @@
+// Internal device-side view of one simulator handle (passed to kernels by value).
+// HBM layout: every per-agent quantity is SoA over ia = env * n_agents + agent so that a warp of
+// consecutive agents reads/writes consecutive addresses; scans are [ia][beam].
+#pragma once
+#include <stdint.h>
+
+enum { F110_P_MU, F110_P_CSF, F110_P_CSR, F110_P_LF, F110_P_LR, F110_P_H, F110_P_M, F110_P_I, F110_P_SMIN,
+       F110_P_SMAX, F110_P_SVMIN, F110_P_SVMAX, F110_P_VSWITCH, F110_P_AMAX, F110_P_VMIN, F110_P_VMAX,
+       F110_P_WIDTH, F110_P_LENGTH, F110_NP };
+
+// EDT tile for the tiled layouts: a 128-byte line holds a 2D patch instead of a row strip.
+//   fp64: 4 x 4 cells,  fp32: 8 x 4 cells (x fastest inside the tile)
+#define F110_T64_W 4
+#define F110_T64_H 4
+#define F110_T32_W 8
+#define F110_T32_H 4
+
+struct F110Dev {
+    int n_envs, n_agents, n_beams, integrator, ego_idx, theta_dis;
+    int noise_mode, auto_reset, count_lookups, n_pool, scan_is_f32;
+    double timestep, fov, eps, max_range, theta_inc, ttc_thresh, noise_std;
+    unsigned long long seed;
+    // map
+    int map_h, map_w, res_pow2, has_rot;
+    int tiles_x64, tiles_x32;          // tiles per row of the tiled layouts
+    double res, inv_res, ox, oy, oc, os, xmax, ymax;
+    double oob64;                      // dt[-1,-1] : value an out-of-map lookup returns
+    float oob32;
+    const double *edt64;               // row-major [h][w]
+    const double *edt64_t;             // tiled
+    const float *edt32_t;              // tiled, in CELL units (metres / res)
+    // tables
+    const double *sines, *cosines;                  // theta_dis
+    const double *scan_angles, *beam_cos, *side_dist;  // n_beams
+    const float2 *dir32;                            // theta_dis: ray direction in cell units per unit cell length
+    const float *beam_cos32, *side_dist32;
+    const double *params;                           // (n_agents + 1) * F110_NP
+    // per (env, agent)
+    double *state;       // [7][NA]
+    double *pose_pre;    // [3][NA] pose after dynamics, before iTTC zeroing (Simulator.agent_poses)
+    double *steer_buf;   // [2][NA] 0 = newest
+    uint8_t *steer_len;  // NA
+    uint8_t *in_collision;
+    void *scans;
+    double *collisions, *collision_idx, *lap_times, *lap_counts;
+    int *toggles;
+    uint8_t *near_start;
+    double *start_x, *start_y;
+    // per env
+    double *start_rot;   // [N][4]
+    double *cur_time;
+    long long *noise_step;
+    uint8_t *done;
+    uint8_t *reset_pending;
+    long long *episode_count;
+    const double *actions;
+    const double *noise;     // [noise_rows][n_beams]
+    long long noise_rows;
+    const double *pool;      // [n_pool][A][3]
+    unsigned long long *lookups;
+    const uint8_t *step_mask;   // [N] or null: envs that take part in this step (masked reset)
+};
+
+// launch helpers implemented in the kernel translation units
+void f110_launch_dynamics(const F110Dev &d, cudaStream_t st);
+void f110_launch_raycast64(const F110Dev &d, int env_begin, int env_count, int variant, cudaStream_t st);
+void f110_launch_raycast32(const F110Dev &d, int env_begin, int env_count, int variant, cudaStream_t st);
+void f110_launch_agents(const F110Dev &d, cudaStream_t st);      // GJK + opponent ray-cast (A >= 2)
+void f110_launch_finalize(const F110Dev &d, cudaStream_t st);    // collisions, lap bookkeeping, done
+void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, double *out, int variant, cudaStream_t st);
+void f110_launch_scan_only32(const F110Dev &d, const double *poses, int n, float *out, int variant, cudaStream_t st);
+void f110_launch_reset(const F110Dev &d, const double *poses_dev, const double *rot_dev, const uint8_t *mask_dev, cudaStream_t st);
+void f110_launch_tile64(const double *src, double *dst, int h, int w, cudaStream_t st);
+void f110_launch_tile32(const double *src, float *dst, int h, int w, double inv_res, cudaStream_t st);

@@ -1,0 +1,765 @@
+// fp64 kernels of the batched F1TENTH step for sm_100a.  Compiled with -fmad=false: the reference
+// (Numba) emits no FMA, and the parity contract needs the same roundings in the same order.
+//
+//   k_dynamics   thread per (env, agent): steer FIFO + pid + RK4/Euler + yaw wrap   (base_classes.py:254-402)
+//   k_raycast64  warp per (env, agent) scan: sphere tracing on the fp64 EDT, noise, iTTC + zeroing
+//                                                                          (laser_models.py:107-217, base_classes.py:227-252)
+//   k_agents     warp per (env, agent), A >= 2: GJK vs every other agent + opponent ray-cast
+//                                                                          (collision_models.py:114-260, laser_models.py:250-346)
+//   k_finalize   thread per env: collision flags, lap bookkeeping, done      (f110_env.py:202-244,292-299)
+//   k_reset      thread per (env, agent)                                     (base_classes.py:181-202, f110_env.py:318-329)
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include "f110_dev.h"
+
+#define FULL 0xffffffffu
+static __device__ __forceinline__ double TWO_PI() { return 6.283185307179586; }
+static __device__ __forceinline__ double PI_() { return 3.141592653589793; }
+
+// ------------------------------------------------------------------------------------------------
+// dynamics (dynamic_models.py)
+// ------------------------------------------------------------------------------------------------
+// dynamic_models.py:29-60
+static __device__ __forceinline__ double accl_constraints(double vel, double accl, double v_switch, double a_max,
+                                                          double v_min, double v_max)
+{
+    double pos_limit = (vel > v_switch) ? a_max * v_switch / vel : a_max;
+    if ((vel <= v_min && accl <= 0) || (vel >= v_max && accl >= 0)) accl = 0.;
+    else if (accl <= -a_max) accl = -a_max;
+    else if (accl >= pos_limit) accl = pos_limit;
+    return accl;
+}
+// dynamic_models.py:62-87
+static __device__ __forceinline__ double steering_constraint(double steer, double sv, double s_min, double s_max,
+                                                             double sv_min, double sv_max)
+{
+    if ((steer <= s_min && sv <= 0) || (steer >= s_max && sv >= 0)) sv = 0.;
+    else if (sv <= sv_min) sv = sv_min;
+    else if (sv >= sv_max) sv = sv_max;
+    return sv;
+}
+
+struct VehP {
+    double mu, C_Sf, C_Sr, lf, lr, h, m, I, s_min, s_max, sv_min, sv_max, v_switch, a_max, v_min, v_max;
+};
+
+// dynamic_models.py:123-176 (kinematic branch :152-160 -> :90-121 re-applies the constraints)
+static __device__ __forceinline__ void dynamics_st(const double x[7], double sv_in, double ac_in, const VehP &p,
+                                                   double f[7])
+{
+    const double g = 9.81;
+    double u0 = steering_constraint(x[2], sv_in, p.s_min, p.s_max, p.sv_min, p.sv_max);
+    double u1 = accl_constraints(x[3], ac_in, p.v_switch, p.a_max, p.v_min, p.v_max);
+    const double lf = p.lf, lr = p.lr, mu = p.mu, m = p.m, I = p.I, h = p.h, C_Sf = p.C_Sf, C_Sr = p.C_Sr;
+    if (fabs(x[3]) < 0.5) {
+        double lwb = lf + lr;
+        double k0 = steering_constraint(x[2], u0, p.s_min, p.s_max, p.sv_min, p.sv_max);
+        double k1 = accl_constraints(x[3], u1, p.v_switch, p.a_max, p.v_min, p.v_max);
+        double s4, c4;
+        sincos(x[4], &s4, &c4);
+        double t2 = tan(x[2]);
+        double c2 = cos(x[2]);
+        f[0] = x[3] * c4;
+        f[1] = x[3] * s4;
+        f[2] = k0;
+        f[3] = k1;
+        f[4] = x[3] / lwb * t2;
+        f[5] = u1 / lwb * t2 + x[3] / (lwb * (c2 * c2)) * u0;
+        f[6] = 0.;
+    } else {
+        double s4, c4;
+        sincos(x[6] + x[4], &s4, &c4);
+        f[0] = x[3] * c4;
+        f[1] = x[3] * s4;
+        f[2] = u0;
+        f[3] = u1;
+        f[4] = x[5];
+        f[5] = -mu * m / (x[3] * I * (lr + lf)) * (lf * lf * C_Sf * (g * lr - u1 * h) + lr * lr * C_Sr * (g * lf + u1 * h)) * x[5]
+             + mu * m / (I * (lr + lf)) * (lr * C_Sr * (g * lf + u1 * h) - lf * C_Sf * (g * lr - u1 * h)) * x[6]
+             + mu * m / (I * (lr + lf)) * lf * C_Sf * (g * lr - u1 * h) * x[2];
+        f[6] = (mu / (x[3] * x[3] * (lr + lf)) * (C_Sr * (g * lf + u1 * h) * lr - C_Sf * (g * lr - u1 * h) * lf) - 1) * x[5]
+             - mu / (x[3] * (lr + lf)) * (C_Sr * (g * lf + u1 * h) + C_Sf * (g * lr - u1 * h)) * x[6]
+             + mu / (x[3] * (lr + lf)) * (C_Sf * (g * lr - u1 * h)) * x[2];
+    }
+}
+
+static __device__ __forceinline__ unsigned pool_index(int e, long long episode, int n_pool)
+{
+    unsigned long long z = (unsigned long long)e * 0x9E3779B97F4A7C15ull + (unsigned long long)episode * 0xBF58476D1CE4E5B9ull;
+    z ^= z >> 31; z *= 0x94D049BB133111EBull; z ^= z >> 29;
+    return (unsigned)(z % (unsigned long long)n_pool);
+}
+
+__global__ void __launch_bounds__(128) k_dynamics(const F110Dev d)
+{
+    const int NA = d.n_envs * d.n_agents;
+    int ia = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ia >= NA) return;
+    int e = ia / d.n_agents, a = ia - e * d.n_agents;
+    if (d.step_mask && !d.step_mask[e]) return;
+
+    double x[7];
+    double raw_steer = d.actions[2 * ia + 0];
+    double vel_cmd = d.actions[2 * ia + 1];
+    int slen = d.steer_len[ia];
+    if (d.auto_reset && d.reset_pending[e]) {
+        // F110Env.reset on the device: the pending env restarts from a pool pose and this step is
+        // the reset's zero-action step (f110_env.py:318-336)
+        unsigned k = pool_index(e, d.episode_count[e], d.n_pool);
+        const double *pp = d.pool + ((size_t)k * d.n_agents + a) * 3;
+        x[0] = pp[0]; x[1] = pp[1]; x[2] = 0.; x[3] = 0.; x[4] = pp[2]; x[5] = 0.; x[6] = 0.;
+        raw_steer = 0.; vel_cmd = 0.; slen = 0;
+        d.near_start[ia] = 1; d.toggles[ia] = 0; d.start_x[ia] = pp[0]; d.start_y[ia] = pp[1];
+        if (a == 0) {
+            const double *pe = d.pool + ((size_t)k * d.n_agents + d.ego_idx) * 3;
+            double sn, cs;
+            sincos(-pe[2], &sn, &cs);
+            double *R = d.start_rot + 4 * (size_t)e;
+            R[0] = cs; R[1] = -sn; R[2] = sn; R[3] = cs;
+            d.cur_time[e] = 0.0;
+            d.noise_step[e] = 0;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 7; i++) x[i] = d.state[(size_t)i * NA + ia];
+    }
+
+    // steering delay FIFO of depth 2 (base_classes.py:268-276)
+    double b0 = d.steer_buf[ia], b1 = d.steer_buf[NA + ia];
+    double steer;
+    if (slen < 2) { steer = 0.; slen += 1; }
+    else { steer = b1; }
+    d.steer_buf[NA + ia] = b0;
+    d.steer_buf[ia] = raw_steer;
+    d.steer_len[ia] = (uint8_t)slen;
+
+    const double *pp = d.params + F110_NP * a;
+    VehP p = { pp[0], pp[1], pp[2], pp[3], pp[4], pp[5], pp[6], pp[7], pp[8], pp[9], pp[10], pp[11], pp[12], pp[13], pp[14], pp[15] };
+
+    // pid (dynamic_models.py:178-221)
+    double sv, accl;
+    {
+        double steer_diff = steer - x[2];
+        if (fabs(steer_diff) > 1e-4) sv = (steer_diff / fabs(steer_diff)) * p.sv_max;
+        else sv = 0.0;
+        double vel_diff = vel_cmd - x[3];
+        double kp;
+        if (x[3] > 0.) kp = (vel_diff > 0) ? 10.0 * p.a_max / p.v_max : 10.0 * p.a_max / (-p.v_min);
+        else kp = (vel_diff > 0) ? 2.0 * p.a_max / p.v_max : 2.0 * p.a_max / (-p.v_min);
+        accl = kp * vel_diff;
+    }
+
+    const double dt = d.timestep;
+    if (d.integrator == 1) {   // RK4 (base_classes.py:282-371)
+        double k1[7], k2[7], k3[7], k4[7], xs[7];
+        dynamics_st(x, sv, accl, p, k1);
+#pragma unroll
+        for (int i = 0; i < 7; i++) xs[i] = x[i] + dt * (k1[i] / 2);
+        dynamics_st(xs, sv, accl, p, k2);
+#pragma unroll
+        for (int i = 0; i < 7; i++) xs[i] = x[i] + dt * (k2[i] / 2);
+        dynamics_st(xs, sv, accl, p, k3);
+#pragma unroll
+        for (int i = 0; i < 7; i++) xs[i] = x[i] + dt * k3[i];
+        dynamics_st(xs, sv, accl, p, k4);
+        const double w = dt * (1.0 / 6.0);
+#pragma unroll
+        for (int i = 0; i < 7; i++) x[i] = x[i] + w * (((k1[i] + 2 * k2[i]) + 2 * k3[i]) + k4[i]);
+    } else {                   // Euler (:373-393)
+        double f[7];
+        dynamics_st(x, sv, accl, p, f);
+#pragma unroll
+        for (int i = 0; i < 7; i++) x[i] = x[i] + dt * f[i];
+    }
+    // single yaw wrap (:398-402)
+    if (x[4] > TWO_PI()) x[4] = x[4] - TWO_PI();
+    else if (x[4] < 0) x[4] = x[4] + TWO_PI();
+
+#pragma unroll
+    for (int i = 0; i < 7; i++) d.state[(size_t)i * NA + ia] = x[i];
+    d.pose_pre[ia] = x[0];
+    d.pose_pre[NA + ia] = x[1];
+    d.pose_pre[2 * (size_t)NA + ia] = x[4];
+}
+
+void f110_launch_dynamics(const F110Dev &d, cudaStream_t st)
+{
+    int NA = d.n_envs * d.n_agents;
+    k_dynamics<<<(NA + 127) / 128, 128, 0, st>>>(d);
+}
+
+// ------------------------------------------------------------------------------------------------
+// lidar: sphere tracing against the EDT (laser_models.py:56-186)
+// ------------------------------------------------------------------------------------------------
+// Truncation of a non-negative double < 2^31 without the (quarter-rate) F2I.F64 path: adding 2^52
+// with round-toward-zero leaves floor(q) in the low mantissa word.  `whole` gets floor(q) as a double.
+static __device__ __forceinline__ int trunc_nonneg(double q, double &whole)
+{
+    double t = __dadd_rz(q, 4503599627370496.0);
+    whole = t - 4503599627370496.0;
+    return __double2loint(t);
+}
+
+// int(x_rot / resolution) of xy_2_rc (laser_models.py:83-84), bit-exact.  When the resolution is a
+// power of two the division is a multiplication.  Otherwise multiply by the rounded reciprocal and
+// redo a true IEEE division only if the product sits within 1e-9 of an integer (the two can then
+// truncate differently; |q*ulp| < 1e-9 for any map below 2^22 cells per side).
+template <bool POW2>
+static __device__ __forceinline__ int cell_index(double v, const F110Dev &d)
+{
+    double q = v * d.inv_res, whole;
+    int c = trunc_nonneg(q, whole);
+    if (!POW2) {
+        double frac = q - whole;
+        if (frac < 1e-9 || frac > 1.0 - 1e-9) c = (int)__ddiv_rn(v, d.res);
+    }
+    return c;
+}
+
+// distance_transform(x, y) (laser_models.py:89-104): out of bounds -> (-1,-1) -> last cell.
+template <bool ROT, bool POW2, bool TILED>
+static __device__ __forceinline__ double edt_lookup(const F110Dev &d, double x, double y)
+{
+    double xt = x - d.ox, yt = y - d.oy;
+    double xr, yr;
+    if (ROT) {
+        xr = xt * d.oc + yt * d.os;
+        yr = -xt * d.os + yt * d.oc;
+    } else {   // origin yaw == 0: x*1 + y*0 is x (bit-exact for finite inputs)
+        xr = xt; yr = yt;
+    }
+    if (xr < 0 || xr >= d.xmax || yr < 0 || yr >= d.ymax) return d.oob64;
+    int c = cell_index<POW2>(xr, d);
+    int r = cell_index<POW2>(yr, d);
+    if (TILED) {
+        unsigned idx = (((unsigned)(r >> 2) * d.tiles_x64 + (unsigned)(c >> 2)) << 4) | ((r & 3) << 2) | (c & 3);
+        return __ldg(d.edt64_t + idx);
+    }
+    return __ldg(d.edt64 + (size_t)r * d.map_w + c);
+}
+
+// Start of the float beam index of get_scan (laser_models.py:166-172)
+static __device__ __forceinline__ double theta_start(const F110Dev &d, double yaw)
+{
+    double td = (double)d.theta_dis;
+    double t = __ddiv_rn(td * (yaw - d.fov / 2.), 2. * PI_());
+    t = fmod(t, td);
+    while (t < 0) t += td;
+    return t;
+}
+
+// Table index of beam i.  The reference accumulates theta_index += increment beam after beam
+// (laser_models.py:180-184) and truncates; the closed form t0 + i*inc differs from that running
+// sum by < 2160 * 2^-43 < 3e-10, so int() can only differ within 1e-9 of an integer -- those beams
+// replay the sequential sum exactly.
+static __device__ __forceinline__ int theta_index_of(const F110Dev &d, double t0, int i)
+{
+    double td = (double)d.theta_dis;
+    double a = t0 + (double)i * d.theta_inc;
+    double whole;
+    int k = trunc_nonneg(a, whole);
+    double frac = a - whole;
+    if (frac < 1e-9 || frac > 1.0 - 1e-9) {
+        double t = t0;
+        for (int j = 0; j < i; j++) {
+            t += d.theta_inc;
+            while (t >= td) t -= td;
+        }
+        return (int)t;
+    }
+    while (k >= d.theta_dis) k -= d.theta_dis;
+    return k;
+}
+
+// trace_ray (laser_models.py:107-146) given the first lookup d0 at the scan origin
+template <bool ROT, bool POW2, bool TILED>
+static __device__ __forceinline__ double trace_ray(const F110Dev &d, double x, double y, double cs, double sn,
+                                                   double d0, unsigned &nlook)
+{
+    double dist = d0, total = d0;
+    while (dist > d.eps && total <= d.max_range) {
+        x += dist * cs;
+        y += dist * sn;
+        dist = edt_lookup<ROT, POW2, TILED>(d, x, y);
+        total += dist;
+        nlook++;
+    }
+    if (total > d.max_range) total = d.max_range;
+    return total;
+}
+
+// iTTC test of one beam (laser_models.py:208-213).  The IEEE division is only issued when the
+// quotient can be inside [0, thresh): |num| > 1.2*thresh*|den| already decides "no".
+static __device__ __forceinline__ bool ttc_hit(double range, double side, double vel, double bcos, double thresh)
+{
+    double proj = vel * bcos;
+    double num = range - side;
+    if (fabs(num) > 1.2 * thresh * fabs(proj)) return false;
+    double ttc = __ddiv_rn(num, proj);
+    return (ttc < thresh) && (ttc >= 0.0);
+}
+
+// One warp per scan, 32 consecutive beams in lockstep per round (adjacent beams hit adjacent EDT
+// cells, so a warp-level gather touches few cache lines); lanes whose ray has converged idle until
+// the round's slowest ray is done.
+template <bool ROT, bool POW2, bool TILED, bool STEP>
+static __device__ __forceinline__ void scan_rounds(const F110Dev &d, double px, double py, double yaw,
+                                                   double *__restrict__ out, const double *__restrict__ noise_row,
+                                                   double vel, bool &hit_any, unsigned &nlook)
+{
+    const int lane = threadIdx.x & 31;
+    const double t0 = theta_start(d, yaw);
+    const double d0 = edt_lookup<ROT, POW2, TILED>(d, px, py);
+    nlook += (lane == 0);
+    for (int base = 0; base < d.n_beams; base += 32) {
+        int i = base + lane;
+        if (i < d.n_beams) {
+            int ti = theta_index_of(d, t0, i);
+            double sn = __ldg(d.sines + ti), cs = __ldg(d.cosines + ti);
+            double r = trace_ray<ROT, POW2, TILED>(d, px, py, cs, sn, d0, nlook);
+            if (noise_row) r += __ldg(noise_row + i);
+            out[i] = r;
+            if (STEP && vel != 0.0)
+                hit_any |= ttc_hit(r, __ldg(d.side_dist + i), vel, __ldg(d.beam_cos + i), d.ttc_thresh);
+        }
+    }
+}
+
+template <bool ROT, bool POW2, bool TILED>
+__global__ void __launch_bounds__(256) k_raycast64(const F110Dev d, int env_begin, int env_count)
+{
+    const int NA = d.n_envs * d.n_agents;
+    int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= env_count * d.n_agents) return;
+    int ia = env_begin * d.n_agents + w;
+    int e = ia / d.n_agents;
+    if (d.step_mask && !d.step_mask[e]) return;
+    const int lane = threadIdx.x & 31;
+    double px = d.state[ia], py = d.state[(size_t)NA + ia];
+    double vel = d.state[3 * (size_t)NA + ia], yaw = d.state[4 * (size_t)NA + ia];
+    const double *noise_row = nullptr;
+    if (d.noise_mode == 1) {
+        long long row = d.noise_step[e];
+        if (row >= d.noise_rows) row %= d.noise_rows;
+        noise_row = d.noise + row * d.n_beams;
+    }
+    bool hit = false;
+    unsigned nlook = 0;
+    scan_rounds<ROT, POW2, TILED, true>(d, px, py, yaw, (double *)d.scans + (size_t)ia * d.n_beams, noise_row, vel, hit, nlook);
+    hit = __any_sync(FULL, hit);
+    // RaceCar.check_ttc (base_classes.py:241-250): state[3:] = 0 -- velocity, YAW, yaw rate, slip
+    if (lane == 0) {
+        if (hit) {
+            d.state[3 * (size_t)NA + ia] = 0.; d.state[4 * (size_t)NA + ia] = 0.;
+            d.state[5 * (size_t)NA + ia] = 0.; d.state[6 * (size_t)NA + ia] = 0.;
+        }
+        d.in_collision[ia] = hit ? 1 : 0;
+    }
+    if (d.count_lookups) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) nlook += __shfl_xor_sync(FULL, nlook, o);
+        if (lane == 0) atomicAdd(d.lookups, (unsigned long long)nlook);
+    }
+}
+
+template <bool ROT, bool POW2, bool TILED>
+__global__ void __launch_bounds__(256) k_scan_only64(const F110Dev d, const double *__restrict__ poses, int n,
+                                                     double *__restrict__ out)
+{
+    int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= n) return;
+    bool hit = false;
+    unsigned nlook = 0;
+    scan_rounds<ROT, POW2, TILED, false>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], out + (size_t)w * d.n_beams,
+                                         nullptr, 0.0, hit, nlook);
+    if (d.count_lookups) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) nlook += __shfl_xor_sync(FULL, nlook, o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(d.lookups, (unsigned long long)nlook);
+    }
+}
+
+#define DISPATCH64(KERNEL, GRID, ...)                                                             \
+    do {                                                                                          \
+        bool tiled = (variant & 1) != 0;                                                          \
+        if (d.has_rot) {                                                                          \
+            if (tiled) KERNEL<true, false, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);              \
+            else KERNEL<true, false, false><<<GRID, 256, 0, st>>>(__VA_ARGS__);                   \
+        } else if (d.res_pow2) {                                                                  \
+            if (tiled) KERNEL<false, true, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);              \
+            else KERNEL<false, true, false><<<GRID, 256, 0, st>>>(__VA_ARGS__);                   \
+        } else {                                                                                  \
+            if (tiled) KERNEL<false, false, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);             \
+            else KERNEL<false, false, false><<<GRID, 256, 0, st>>>(__VA_ARGS__);                  \
+        }                                                                                         \
+    } while (0)
+
+void f110_launch_raycast64(const F110Dev &d, int env_begin, int env_count, int variant, cudaStream_t st)
+{
+    long long warps = (long long)env_count * d.n_agents;
+    int grid = (int)((warps * 32 + 255) / 256);
+    if (grid == 0) return;
+    DISPATCH64(k_raycast64, grid, d, env_begin, env_count);
+}
+
+void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, double *out, int variant, cudaStream_t st)
+{
+    int grid = (int)(((long long)n * 32 + 255) / 256);
+    if (grid == 0) return;
+    DISPATCH64(k_scan_only64, grid, d, poses, n, out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// multi-agent: GJK + opponent ray-cast (collision_models.py, laser_models.py:220-346)
+// ------------------------------------------------------------------------------------------------
+// collision_models.py:219-260: corners rl, rr, fr, fl of the car rectangle
+static __device__ __forceinline__ void get_vertices(double x, double y, double th, double length, double width,
+                                                    double v[4][2])
+{
+    double sn, c;
+    sincos(th, &sn, &c);
+    const double hl = length / 2, hw = width / 2;
+    const double lx[4] = { -hl, -hl, hl, hl };
+    const double ly[4] = { hw, -hw, -hw, hw };
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        v[k][0] = (c * lx[k] + (-sn) * ly[k]) + x;
+        v[k][1] = (sn * lx[k] + c * ly[k]) + y;
+    }
+}
+
+// np.argmax(vertices.dot(d)) -- first maximum (collision_models.py:82-92)
+static __device__ __forceinline__ int furthest(const double v[4][2], double dx, double dy)
+{
+    int best = 0;
+    double bv = v[0][0] * dx + v[0][1] * dy;
+#pragma unroll
+    for (int k = 1; k < 4; k++) {
+        double t = v[k][0] * dx + v[k][1] * dy;
+        if (t > bv) { bv = t; best = k; }
+    }
+    return best;
+}
+static __device__ __forceinline__ void support(const double v1[4][2], const double v2[4][2], double dx, double dy,
+                                               double &ox, double &oy)
+{
+    int i = furthest(v1, dx, dy), j = furthest(v2, -dx, -dy);
+    // register-resident select instead of dynamic indexing
+    double ax = v1[0][0], ay = v1[0][1], bx = v2[0][0], by = v2[0][1];
+#pragma unroll
+    for (int k = 1; k < 4; k++) {
+        if (i == k) { ax = v1[k][0]; ay = v1[k][1]; }
+        if (j == k) { bx = v2[k][0]; by = v2[k][1]; }
+    }
+    ox = ax - bx; oy = ay - by;
+}
+// tripleProduct(a, b, c) = b*(a.c) - a*(b.c)   (collision_models.py:52-64)
+static __device__ __forceinline__ void triple(double ax, double ay, double bx, double by, double cx, double cy,
+                                              double &ox, double &oy)
+{
+    double ac = ax * cx + ay * cy, bc = bx * cx + by * cy;
+    ox = bx * ac - ax * bc;
+    oy = by * ac - ay * bc;
+}
+
+// collision (GJK, collision_models.py:114-182); simplex kept in registers as s0, s1 (+ the new point a)
+static __device__ bool gjk_collision(const double v1[4][2], const double v2[4][2])
+{
+    double p1x = (((v1[0][0] + v1[1][0]) + v1[2][0]) + v1[3][0]) / 4, p1y = (((v1[0][1] + v1[1][1]) + v1[2][1]) + v1[3][1]) / 4;
+    double p2x = (((v2[0][0] + v2[1][0]) + v2[2][0]) + v2[3][0]) / 4, p2y = (((v2[0][1] + v2[1][1]) + v2[2][1]) + v2[3][1]) / 4;
+    double dx = p1x - p2x, dy = p1y - p2y;
+    if (dx == 0 && dy == 0) dx = 1.0;
+    double ax, ay;
+    support(v1, v2, dx, dy, ax, ay);
+    double s0x = ax, s0y = ay, s1x = 0, s1y = 0;
+    if (dx * ax + dy * ay <= 0) return false;
+    dx = -ax; dy = -ay;
+    int index = 0, iter_count = 0;
+    while (iter_count < 1000) {
+        support(v1, v2, dx, dy, ax, ay);
+        index += 1;
+        if (dx * ax + dy * ay <= 0) return false;
+        double aox = -ax, aoy = -ay;
+        if (index < 2) {
+            s1x = ax; s1y = ay;                 // simplex[1] = a
+            double abx = s0x - ax, aby = s0y - ay;
+            triple(abx, aby, aox, aoy, abx, aby, dx, dy);
+            if (sqrt(dx * dx + dy * dy) < 1e-10) { dx = aby; dy = -1 * abx; }
+            continue;
+        }
+        // index == 2: simplex = {s0 (c), s1 (b), a}
+        double abx = s1x - ax, aby = s1y - ay, acx = s0x - ax, acy = s0y - ay;
+        double px, py;
+        triple(abx, aby, acx, acy, acx, acy, px, py);          // acperp
+        if (px * aox + py * aoy >= 0) {
+            dx = px; dy = py;
+        } else {
+            triple(acx, acy, abx, aby, abx, aby, px, py);      // abperp
+            if (px * aox + py * aoy < 0) return true;
+            s0x = s1x; s0y = s1y;                               // simplex[0] = simplex[1]
+            dx = px; dy = py;
+        }
+        s1x = ax; s1y = ay;                                     // simplex[1] = simplex[2]
+        index -= 1;
+        iter_count += 1;
+    }
+    return false;
+}
+
+// get_range (laser_models.py:250-280)
+static __device__ __forceinline__ double get_range(double ox_, double oy_, double v3x, double v3y, double vax,
+                                                   double vay, double vbx, double vby)
+{
+    double v1x = ox_ - vax, v1y = oy_ - vay;
+    double v2x = vbx - vax, v2y = vby - vay;
+    double denom = v2x * v3x + v2y * v3y;
+    double distance = CUDART_INF;
+    if (fabs(denom) > 0.0) {
+        double d1 = __ddiv_rn(v2x * v1y - v2y * v1x, denom);
+        double d2 = __ddiv_rn(v1x * v3x + v1y * v3y, denom);
+        if (d1 >= 0.0 && d2 >= 0.0 && d2 <= 1.0) distance = d1;
+    } else {
+        double bax = vax - ox_, bay = vay - oy_, cax = ox_ - vbx, cay = oy_ - vby;
+        if (fabs(bax * cay - bay * cax) < 1e-8) {
+            double da = sqrt(bax * bax + bay * bay);
+            double db = sqrt(cax * cax + cay * cay);
+            distance = da < db ? da : db;
+        }
+    }
+    return distance;
+}
+
+// int(np.argmin(|scan_angles - target|)) (laser_models.py:310-313): scan_angles is an arithmetic
+// progression, so the minimum is next to round((target - a0)/inc); the table decides ties exactly.
+static __device__ __forceinline__ int nearest_beam(const F110Dev &d, double target)
+{
+    if (target != target) return 0;                 // np.argmin returns the first NaN
+    const int B = d.n_beams;
+    double a0 = __ldg(d.scan_angles);
+    double inc = d.fov / (double)(B - 1);
+    double g = (target - a0) / inc;
+    int k = (g <= 0.) ? 0 : (g >= (double)(B - 1) ? B - 1 : (int)(g + 0.5));
+    int lo = max(0, k - 2), hi = min(B - 1, k + 2);
+    int best = lo;
+    double bv = fabs(__ldg(d.scan_angles + lo) - target);
+    for (int i = lo + 1; i <= hi; i++) {
+        double t = fabs(__ldg(d.scan_angles + i) - target);
+        if (t < bv) { bv = t; best = i; }
+    }
+    return best;
+}
+
+template <typename SCAN_T>
+__global__ void __launch_bounds__(128) k_agents(const F110Dev d)
+{
+    const int NA = d.n_envs * d.n_agents, A = d.n_agents;
+    int ia = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (ia >= NA) return;
+    const int lane = threadIdx.x & 31;
+    int e = ia / A, a = ia - e * A;
+    if (d.step_mask && !d.step_mask[e]) return;
+    const size_t base = (size_t)e * A;
+    // Simulator.check_collision (base_classes.py:529-543) on the pre-iTTC poses with the construct-time
+    // car size: lane o tests the pair (min(a,o), max(a,o)); collision_idx = last writer = largest partner
+    const double gw = d.params[F110_NP * A + 0], gl = d.params[F110_NP * A + 1];
+    bool hit = false;
+    if (lane < A && lane != a) {
+        int i = min(a, lane), j = max(a, lane);
+        double vi[4][2], vj[4][2];
+        get_vertices(d.pose_pre[base + i], d.pose_pre[NA + base + i], d.pose_pre[2 * (size_t)NA + base + i], gl, gw, vi);
+        get_vertices(d.pose_pre[base + j], d.pose_pre[NA + base + j], d.pose_pre[2 * (size_t)NA + base + j], gl, gw, vj);
+        hit = gjk_collision(vi, vj);
+    }
+    unsigned hits = __ballot_sync(FULL, hit);
+    if (lane == 0) {
+        d.collision_idx[ia] = hits ? (double)(31 - __clz(hits)) : -1.0;
+        d.collisions[ia] = (hits || d.in_collision[ia]) ? 1.0 : 0.0;
+    }
+    // RaceCar.ray_cast_agents (base_classes.py:204-225): own pose AFTER iTTC zeroing, opponents' poses
+    // from before it, opponents drawn with THIS agent's length/width
+    const double px = d.state[ia], py = d.state[(size_t)NA + ia], yaw = d.state[4 * (size_t)NA + ia];
+    const double len = d.params[F110_NP * a + F110_P_LENGTH], wid = d.params[F110_NP * a + F110_P_WIDTH];
+    SCAN_T *scan = (SCAN_T *)d.scans + (size_t)ia * d.n_beams;
+    double esn, ecs;
+    sincos(yaw, &esn, &ecs);
+    const double ego_ang = atan2(esn, ecs);
+    for (int o = 0; o < A; o++) {
+        if (o == a) continue;
+        double v[4][2];
+        get_vertices(d.pose_pre[base + o], d.pose_pre[NA + base + o], d.pose_pre[2 * (size_t)NA + base + o], len, wid, v);
+        // get_blocked_view_indices (laser_models.py:283-315)
+        int mn = 0x7fffffff, mx = -1;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            double vx = v[k][0] - px, vy = v[k][1] - py;
+            double nrm = sqrt(vx * vx + vy * vy);
+            double angle = ego_ang - atan2(vy / nrm, vx / nrm);
+            if (angle > PI_()) angle = angle - 2 * PI_();
+            else if (angle < -PI_()) angle = angle + 2 * PI_();
+            int b = nearest_beam(d, -angle);
+            mn = min(mn, b); mx = max(mx, b);
+        }
+        // ray_cast (laser_models.py:318-346): beams [mn, mx] x 4 edges, in place
+        for (int i = mn + lane; i <= mx; i += 32) {
+            double bt = yaw + __ldg(d.scan_angles + i);
+            double v3s, v3c;
+            sincos(bt + PI_() / 2., &v3s, &v3c);
+            double r = (double)scan[i];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                double rr = get_range(px, py, v3c, v3s, v[j][0], v[j][1], v[(j + 1) & 3][0], v[(j + 1) & 3][1]);
+                if (rr < r) r = rr;
+            }
+            scan[i] = (SCAN_T)r;
+        }
+    }
+}
+
+void f110_launch_agents(const F110Dev &d, cudaStream_t st)
+{
+    long long NA = (long long)d.n_envs * d.n_agents;
+    int grid = (int)((NA * 32 + 127) / 128);
+    if (d.scan_is_f32) k_agents<float><<<grid, 128, 0, st>>>(d);
+    else k_agents<double><<<grid, 128, 0, st>>>(d);
+}
+
+// ------------------------------------------------------------------------------------------------
+// F110Env.step tail: time, _check_done (f110_env.py:202-244, 292-299)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_finalize(const F110Dev d)
+{
+    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= d.n_envs) return;
+    if (d.step_mask && !d.step_mask[e]) return;
+    const int A = d.n_agents, NA = d.n_envs * A;
+    double t = d.cur_time[e] + d.timestep;
+    d.cur_time[e] = t;
+    d.noise_step[e] += 1;
+    const double *R = d.start_rot + 4 * (size_t)e;
+    const double r0 = R[0], r1 = R[1], r2 = R[2], r3 = R[3];
+    bool all_done = true;
+    for (int a = 0; a < A; a++) {
+        size_t ia = (size_t)e * A + a;
+        if (A == 1) {   // no GJK pass: collisions = iTTC flag (base_classes.py:581-582)
+            d.collisions[ia] = d.in_collision[ia] ? 1.0 : 0.0;
+            d.collision_idx[ia] = -1.0;
+        }
+        double dx = d.state[ia] - d.start_x[ia];
+        double dy = d.state[(size_t)NA + ia] - d.start_y[ia];
+        double d0 = r0 * dx + r1 * dy;
+        double ty = r2 * dx + r3 * dy;
+        if (ty > 2) ty -= 2;
+        else if (ty < -2) ty = -2 - ty;
+        else ty = 0;
+        double dist2 = d0 * d0 + ty * ty;
+        bool closes = dist2 <= 0.1;
+        int tg = d.toggles[ia];
+        bool near = d.near_start[ia] != 0;
+        if (closes && !near) { near = true; tg += 1; }
+        else if (!closes && near) { near = false; tg += 1; }
+        d.near_start[ia] = near ? 1 : 0;
+        d.toggles[ia] = tg;
+        d.lap_counts[ia] = (double)(tg / 2);
+        if (tg < 4) d.lap_times[ia] = t;
+        if (tg < 4) all_done = false;
+    }
+    bool done = (d.collisions[(size_t)e * A + d.ego_idx] != 0.0) || all_done;
+    d.done[e] = done ? 1 : 0;
+    if (d.auto_reset) {
+        d.reset_pending[e] = done ? 1 : 0;
+        if (done) d.episode_count[e] += 1;
+    }
+}
+
+void f110_launch_finalize(const F110Dev &d, cudaStream_t st)
+{
+    k_finalize<<<(d.n_envs + 127) / 128, 128, 0, st>>>(d);
+}
+
+// ------------------------------------------------------------------------------------------------
+// F110Env.reset / RaceCar.reset (f110_env.py:318-332, base_classes.py:181-202); the zero-action
+// step that follows (:335-336) is issued by the host wrapper.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_reset(const F110Dev d, const double *__restrict__ poses,
+                                               const double *__restrict__ rot, const uint8_t *__restrict__ mask)
+{
+    const int A = d.n_agents, NA = d.n_envs * A;
+    int ia = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ia >= NA) return;
+    int e = ia / A, a = ia - e * A;
+    if (mask && !mask[e]) return;
+    const double *p = poses + 3 * (size_t)ia;
+    d.state[ia] = p[0];
+    d.state[(size_t)NA + ia] = p[1];
+    d.state[2 * (size_t)NA + ia] = 0.;
+    d.state[3 * (size_t)NA + ia] = 0.;
+    d.state[4 * (size_t)NA + ia] = p[2];
+    d.state[5 * (size_t)NA + ia] = 0.;
+    d.state[6 * (size_t)NA + ia] = 0.;
+    d.steer_len[ia] = 0;
+    d.in_collision[ia] = 0;
+    d.collisions[ia] = 0.;
+    d.near_start[ia] = 1;
+    d.toggles[ia] = 0;
+    d.start_x[ia] = p[0];
+    d.start_y[ia] = p[1];
+    if (a == 0) {
+        double *R = d.start_rot + 4 * (size_t)e;
+        if (rot) {
+            R[0] = rot[4 * e]; R[1] = rot[4 * e + 1]; R[2] = rot[4 * e + 2]; R[3] = rot[4 * e + 3];
+        } else {
+            double sn, cs;
+            sincos(-poses[3 * ((size_t)e * A + d.ego_idx) + 2], &sn, &cs);
+            R[0] = cs; R[1] = -sn; R[2] = sn; R[3] = cs;
+        }
+        d.cur_time[e] = 0.0;
+        d.noise_step[e] = 0;
+        d.done[e] = 0;
+        d.reset_pending[e] = 0;
+        d.episode_count[e] += 1;
+    }
+}
+
+void f110_launch_reset(const F110Dev &d, const double *poses_dev, const double *rot_dev, const uint8_t *mask_dev,
+                       cudaStream_t st)
+{
+    int NA = d.n_envs * d.n_agents;
+    k_reset<<<(NA + 127) / 128, 128, 0, st>>>(d, poses_dev, rot_dev, mask_dev);
+}
+
+// ------------------------------------------------------------------------------------------------
+// EDT re-layout: row-major fp64 -> 2D tiles so that one 128-byte line is a 4x4 (fp64) / 8x4 (fp32)
+// patch of cells; the fp32 copy is stored in CELL units (metres / resolution).
+// ------------------------------------------------------------------------------------------------
+__global__ void k_tile64(const double *__restrict__ src, double *__restrict__ dst, int h, int w, int tiles_x)
+{
+    int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y * blockDim.y + threadIdx.y;
+    int wp = tiles_x * F110_T64_W;
+    int hp = ((h + F110_T64_H - 1) / F110_T64_H) * F110_T64_H;
+    if (c >= wp || r >= hp) return;
+    double v = (c < w && r < h) ? src[(size_t)r * w + c] : 0.0;
+    size_t idx = (((size_t)(r >> 2) * tiles_x + (c >> 2)) << 4) | ((r & 3) << 2) | (c & 3);
+    dst[idx] = v;
+}
+__global__ void k_tile32(const double *__restrict__ src, float *__restrict__ dst, int h, int w, int tiles_x, double inv_res)
+{
+    int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y * blockDim.y + threadIdx.y;
+    int wp = tiles_x * F110_T32_W;
+    int hp = ((h + F110_T32_H - 1) / F110_T32_H) * F110_T32_H;
+    if (c >= wp || r >= hp) return;
+    double v = (c < w && r < h) ? src[(size_t)r * w + c] * inv_res : 0.0;
+    size_t idx = (((size_t)(r >> 2) * tiles_x + (c >> 3)) << 5) | ((r & 3) << 3) | (c & 7);
+    dst[idx] = (float)v;
+}
+void f110_launch_tile64(const double *src, double *dst, int h, int w, cudaStream_t st)
+{
+    int tiles_x = (w + F110_T64_W - 1) / F110_T64_W;
+    dim3 b(32, 8), g((tiles_x * F110_T64_W + 31) / 32, (h + F110_T64_H + 7) / 8);
+    k_tile64<<<g, b, 0, st>>>(src, dst, h, w, tiles_x);
+}
+void f110_launch_tile32(const double *src, float *dst, int h, int w, double inv_res, cudaStream_t st)
+{
+    int tiles_x = (w + F110_T32_W - 1) / F110_T32_W;
+    dim3 b(32, 8), g((tiles_x * F110_T32_W + 31) / 32, (h + F110_T32_H + 7) / 8);
+    k_tile32<<<g, b, 0, st>>>(src, dst, h, w, tiles_x, inv_res);
+}

@@ -1,0 +1,132 @@
+"""Host-side setup for the batched simulator: map -> EDT, lookup tables, noise rows, params.
+
+Setup-time work the reference also does on the host (ScanSimulator2D.__init__/set_map,
+RaceCar.__init__); the arrays are uploaded once through the C ABI.  Values must be
+bit-identical to the reference's so that cell indices and iTTC flags match, hence numpy
+float64 throughout and the same formulas (cited per function).
+"""
+import os
+
+import numpy as np
+
+from ._native import PARAM_KEYS
+
+MAPS_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "maps")
+
+# reference default vehicle (f110_env.py:128)
+DEFAULT_PARAMS = {"mu": 1.0489, "C_Sf": 4.718, "C_Sr": 5.4562, "lf": 0.15875, "lr": 0.17145, "h": 0.074,
+                  "m": 3.74, "I": 0.04712, "s_min": -0.4189, "s_max": 0.4189, "sv_min": -3.2, "sv_max": 3.2,
+                  "v_switch": 7.319, "a_max": 9.51, "v_min": -5.0, "v_max": 20.0, "width": 0.31, "length": 0.58}
+
+
+def resolve_map(map_name):
+    """kwargs['map'] -> yaml path, as F110Env.__init__ does (f110_env.py:106-118): bundled names map to
+    the packaged yaml, anything else is '<map>.yaml'."""
+    if map_name is None:
+        return os.path.join(MAPS_DIR, "vegas.yaml")
+    if map_name in ("berlin", "skirk", "levine"):
+        return os.path.join(MAPS_DIR, map_name + ".yaml")
+    return map_name + ".yaml"
+
+
+class MapData(object):
+    """Occupancy image -> metric EDT (ScanSimulator2D.set_map, laser_models.py:383-427)."""
+
+    def __init__(self, map_path, map_ext):
+        import yaml
+        from PIL import Image
+        from scipy.ndimage import distance_transform_edt
+        img_path = os.path.splitext(map_path)[0] + map_ext
+        occ = np.asarray(Image.open(img_path).transpose(Image.FLIP_TOP_BOTTOM), dtype=np.float64)
+        free = occ > 128.0                                   # <=128 -> obstacle, >128 -> free (:403-404)
+        with open(map_path, "r") as stream:
+            meta = yaml.safe_load(stream)
+        self.resolution = float(meta["resolution"])
+        origin = meta["origin"]
+        self.origin = (float(origin[0]), float(origin[1]), float(origin[2]))
+        self.orig_c = float(np.cos(origin[2]))
+        self.orig_s = float(np.sin(origin[2]))
+        self.height, self.width = occ.shape[0], occ.shape[1]
+        # get_dt (laser_models.py:40-53): exact Euclidean distance to the nearest obstacle pixel, metres
+        self.edt = np.ascontiguousarray(self.resolution * distance_transform_edt(free))
+        self.path = map_path
+        self.ext = map_ext
+
+    @classmethod
+    def from_arrays(cls, edt, resolution, origin=(0.0, 0.0, 0.0)):
+        self = cls.__new__(cls)
+        self.edt = np.ascontiguousarray(edt, dtype=np.float64)
+        self.height, self.width = self.edt.shape
+        self.resolution = float(resolution)
+        self.origin = tuple(float(o) for o in origin)
+        self.orig_c = float(np.cos(origin[2]))
+        self.orig_s = float(np.sin(origin[2]))
+        self.path = None
+        self.ext = None
+        return self
+
+
+def trig_tables(theta_dis=2000):
+    """sin/cos of np.linspace(0, 2*pi, theta_dis) -- endpoint included (laser_models.py:379-381)."""
+    theta = np.linspace(0.0, 2 * np.pi, num=theta_dis)
+    return np.sin(theta), np.cos(theta)
+
+
+def beam_tables(num_beams, fov, params):
+    """Per-beam angle, cosine and lidar-to-hull distance (RaceCar.__init__, base_classes.py:120-156)."""
+    inc = fov / (num_beams - 1)
+    ang = -fov / 2. + np.arange(num_beams) * inc
+    cosines = np.cos(ang)
+    half_w = params["width"] / 2.
+    half_l = (params["lf"] + params["lr"]) / 2.
+    # each quadrant folds onto the first one: distance along the beam to the side and to the front/rear
+    with np.errstate(divide="ignore", invalid="ignore"):
+        q1 = (ang > 0) & (ang < np.pi / 2)
+        q2 = (ang > 0) & ~(ang < np.pi / 2)
+        q4 = ~(ang > 0) & (ang > -np.pi / 2)
+        q3 = ~(ang > 0) & ~(ang > -np.pi / 2)
+        to_side = np.empty(num_beams)
+        to_fr = np.empty(num_beams)
+        to_side[q1] = half_w / np.sin(ang[q1]);               to_fr[q1] = half_l / np.cos(ang[q1])
+        to_side[q2] = half_w / np.cos(ang[q2] - np.pi / 2.);  to_fr[q2] = half_l / np.sin(ang[q2] - np.pi / 2.)
+        to_side[q4] = half_w / np.sin(-ang[q4]);              to_fr[q4] = half_l / np.cos(-ang[q4])
+        to_side[q3] = half_w / np.cos(-ang[q3] - np.pi / 2);  to_fr[q3] = half_l / np.sin(-ang[q3] - np.pi / 2)
+    side = np.minimum(to_side, to_fr)
+    return ang, cosines, side
+
+
+def noise_rows(seed, first, count, num_beams, std_dev=0.01):
+    """Rows [first, first+count) of the per-car noise stream: row k is the k-th
+    `default_rng(seed).normal(0., std, size=B)` draw after a reset (base_classes.py:202, laser_models.py:451).
+    PCG64 + ziggurat is sequential, so rows are regenerated from the start of the stream."""
+    rng = np.random.default_rng(seed=seed)
+    out = np.empty((first + count, num_beams))
+    for k in range(first + count):
+        out[k] = rng.normal(0., std_dev, size=num_beams)
+    return out[first:]
+
+
+def params_vector(params):
+    missing = [k for k in PARAM_KEYS if k not in params]
+    if missing:
+        raise KeyError("vehicle params missing keys: %s" % missing)
+    return np.array([float(params[k]) for k in PARAM_KEYS], dtype=np.float64)
+
+
+def start_rotation(theta_ego):
+    """Rotation by -theta_ego, elementwise like f110_env.py:329; theta_ego: (N,) -> (N, 4) row-major."""
+    t = np.asarray(theta_ego, dtype=np.float64)
+    return np.ascontiguousarray(np.stack([np.cos(-t), -np.sin(-t), np.sin(-t), np.cos(-t)], axis=-1))
+
+
+def raceline_poses(n, csv_path=None, lateral=0.0, seed=0):
+    """n start poses spread along the example_map raceline (x, y, psi + pi/2) -- SURVEY 8d config 2."""
+    csv_path = csv_path or os.path.join(MAPS_DIR, "example_waypoints.csv")
+    wp = np.loadtxt(csv_path, delimiter=";", skiprows=3)
+    idx = (np.arange(n) * wp.shape[0]) // n
+    poses = np.stack([wp[idx, 1], wp[idx, 2], wp[idx, 3] + np.pi / 2], axis=1)
+    if lateral:
+        off = np.random.default_rng(seed).uniform(-lateral, lateral, n)
+        poses[:, 0] += -off * np.sin(poses[:, 2])
+        poses[:, 1] += off * np.cos(poses[:, 2])
+    return poses

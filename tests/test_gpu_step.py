@@ -1,0 +1,191 @@
+"""GPU parity of the whole step (dynamics, lidar, iTTC, GJK, opponent ray-cast, laps) through the C ABI:
+against the reference goldens and, at BASELINE config sizes, against the CPU oracle."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import f110_oracle as fo
+from conftest import GOLDEN, MAPS
+
+pytestmark = pytest.mark.gpu
+ROLLOUT_FILES = sorted(glob.glob(os.path.join(GOLDEN, "rollout_*.npz")))
+REL = 1e-9      # north_star: fp64 poses and velocities <= 1e-9 relative after 1000 steps
+SCAN_TOL = 1e-4  # metres
+
+
+def _state(env):
+    return env.state.permute(1, 2, 0).cpu().numpy()
+
+
+def _close(a, b, rel=REL):
+    return np.abs(a - b) <= rel * np.maximum(1.0, np.abs(b))
+
+
+@pytest.mark.parametrize("path", ROLLOUT_FILES, ids=[os.path.basename(p)[:-4] for p in ROLLOUT_FILES])
+def test_rollouts_match_reference_goldens(path):
+    from red_gym_b200 import BatchF110Env
+    d = np.load(path)
+    A = int(d["num_agents"])
+    N, T = d["poses0"].shape[0], d["actions"].shape[0]
+    env = BatchF110Env(num_envs=N, num_agents=A, map=os.path.join(MAPS, str(d["map"])), fov=float(d["fov"]),
+                       integrator=str(d["integrator"]), seed=int(d["seed"]))
+    obs, rew, done, info = env.reset(d["poses0"])
+    assert rew == 0.01
+    steps = list(d["scan_steps"])
+    for t in range(T + 1):
+        if t > 0:
+            obs, rew, done, info = env.step(d["actions"][t - 1])
+        # bit-exact: flags and counters
+        assert (env.collisions.cpu().numpy() == d["collisions"][:, t]).all(), t
+        assert (env.collision_idx.cpu().numpy() == d["collision_idx"][:, t]).all(), t
+        assert (env.toggle_list.cpu().numpy() == d["toggles"][:, t]).all(), t
+        assert (env.lap_counts.cpu().numpy() == d["lap_counts"][:, t]).all(), t
+        assert (done.cpu().numpy() == d["done"][:, t]).all(), t
+        assert _close(env.lap_times.cpu().numpy(), d["lap_times"][:, t], 1e-12).all(), t
+        assert _close(_state(env), d["states"][:, t]).all(), (t, np.abs(_state(env) - d["states"][:, t]).max())
+        op = d["obs_pose"][:, t]
+        assert _close(obs["poses_x"].cpu().numpy(), op[..., 0]).all() and _close(obs["poses_theta"].cpu().numpy(), op[..., 2]).all()
+        assert _close(obs["linear_vels_x"].cpu().numpy(), op[..., 3]).all() and _close(obs["ang_vels_z"].cpu().numpy(), op[..., 4]).all()
+        assert np.abs(obs["scans"].cpu().numpy().sum(axis=2) - d["scan_sum"][:, t]).max() <= 1080 * SCAN_TOL
+        if t in steps:
+            assert np.abs(obs["scans"].cpu().numpy() - d["scans"][:, steps.index(t)]).max() <= SCAN_TOL, t
+    assert (info["checkpoint_done"].cpu().numpy() == (d["toggles"][:, -1] >= 4)).all()
+
+
+def _run_against_oracle(N, A, T, poses, actions, check_every, integrator="RK4", seed=12345):
+    from red_gym_b200 import BatchF110Env
+    kw = dict(map=os.path.join(MAPS, "example_map"), integrator=integrator, seed=seed)
+    env = BatchF110Env(num_envs=N, num_agents=A, **kw)
+    ora = fo.OracleEnv(N, A, noise_rows=T + 8, **kw)
+    env.reset(poses)
+    ora.reset(poses)
+    diverged = np.zeros(N, dtype=bool)    # envs whose discrete events (iTTC / GJK / lap) fell on the other side of a threshold
+    for t in range(T):
+        env.step(actions[t])
+        ora.step(actions[t])
+        if (t + 1) % check_every == 0 or t == T - 1:
+            flags_ok = (env.collisions.cpu().numpy() == ora.collisions).all(axis=1) & \
+                       (env.toggle_list.cpu().numpy() == ora.toggles).all(axis=1) & \
+                       (env.collision_idx.cpu().numpy() == ora.collision_idx).all(axis=1)
+            st_ok = _close(_state(env), ora.state).all(axis=(1, 2))
+            diverged |= ~(flags_ok & st_ok)
+    scans_ok = np.abs(env.scans.cpu().numpy() - ora.scans).max(axis=(1, 2)) <= SCAN_TOL
+    return env, ora, diverged, scans_ok
+
+
+def test_config2_4096_envs_1000_steps_vs_oracle():
+    """BASELINE config 2: 4096 single-agent envs on example_map, random actions (default_rng(2024)), RK4, numpy noise."""
+    from red_gym_b200.host import raceline_poses
+    N, T = 4096, 1000
+    poses = raceline_poses(N)[:, None, :]
+    rng = np.random.default_rng(2024)
+    actions = np.stack([rng.uniform(-0.4189, 0.4189, (T, N, 1)), rng.uniform(0.0, 8.0, (T, N, 1))], axis=-1)
+    env, ora, diverged, scans_ok = _run_against_oracle(N, 1, T, poses, actions, 50)
+    # every env crashes within 1000 random steps; a 1-ulp sin/cos difference may move a crash by a step in a few
+    bad = np.flatnonzero(diverged)
+    assert bad.size <= N // 1000, "envs diverged at a discontinuity: %s" % bad[:20]
+    ok = ~diverged
+    assert (env.collisions.cpu().numpy()[ok] == ora.collisions[ok]).all()
+    assert (env.lap_counts.cpu().numpy()[ok] == ora.lap_counts[ok]).all()
+    assert scans_ok[ok].all()
+    assert _close(_state(env)[ok], ora.state[ok]).all()
+    assert ora.collisions.sum() > N // 2       # the workload does exercise iTTC
+
+
+def test_config4_two_agents_vs_oracle():
+    """BASELINE config 4 (subset): head-to-head pairs, chaser 1.5 m behind with lateral offset; GJK + opponent ray-cast."""
+    from red_gym_b200.host import raceline_poses
+    N, T = 1024, 300
+    rng = np.random.default_rng(4)
+    lead = raceline_poses(N)
+    lat = rng.uniform(-0.3, 0.3, N)
+    chase = lead.copy()
+    chase[:, 0] += -1.5 * np.cos(lead[:, 2]) - lat * np.sin(lead[:, 2])
+    chase[:, 1] += -1.5 * np.sin(lead[:, 2]) + lat * np.cos(lead[:, 2])
+    poses = np.stack([lead, chase], axis=1)
+    actions = np.zeros((T, N, 2, 2))
+    actions[..., 0] = rng.uniform(-0.15, 0.15, (T // 20 + 1, N, 2)).repeat(20, axis=0)[:T]
+    actions[:, :, 0, 1] = rng.uniform(0.0, 4.0, (T // 20 + 1, N)).repeat(20, axis=0)[:T]
+    actions[:, :, 1, 1] = rng.uniform(2.0, 8.0, (T // 20 + 1, N)).repeat(20, axis=0)[:T]
+    env, ora, diverged, scans_ok = _run_against_oracle(N, 2, T, poses, actions, 10)
+    bad = np.flatnonzero(diverged)
+    assert bad.size <= 2, "envs diverged at a discontinuity: %s" % bad[:20]
+    ok = ~diverged
+    assert scans_ok[ok].all()
+    assert (ora.collision_idx >= 0).any()      # GJK did fire
+
+
+def test_masked_reset_and_param_update():
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses, DEFAULT_PARAMS
+    N = 64
+    kw = dict(map=os.path.join(MAPS, "example_map"))
+    env = BatchF110Env(num_envs=N, num_agents=1, **kw)
+    ora = fo.OracleEnv(N, 1, **kw)
+    poses = raceline_poses(N)[:, None, :]
+    env.reset(poses); ora.reset(poses)
+    rng = np.random.default_rng(1)
+    p2 = dict(DEFAULT_PARAMS); p2["mu"] = 0.8; p2["m"] = 3.2
+    for t in range(120):
+        act = np.stack([rng.uniform(-0.3, 0.3, (N, 1)), rng.uniform(0.0, 7.0, (N, 1))], axis=-1)
+        env.step(act); ora.step(act)
+        if t == 40:
+            env.update_params(p2); ora.set_params(p2)
+        if t % 30 == 29:      # reset the envs that are done, leave the others running
+            mask = ora.done.astype(bool).copy()
+            if mask.any():
+                env.reset(poses, mask=mask); ora.reset(poses, mask=mask)
+    assert _close(_state(env), ora.state).all()
+    assert (env.collisions.cpu().numpy() == ora.collisions).all()
+    assert (env.noise_step.cpu().numpy() == ora.noise_step).all()
+    with pytest.raises(IndexError):
+        env.update_params(p2, index=5)
+    with pytest.raises(ValueError):
+        env.reset(np.zeros((N, 2, 3)))
+
+
+def test_auto_reset_fast_path_runs_and_restarts():
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    import torch
+    N = 2048
+    pool = raceline_poses(512)[:, None, :]
+    env = BatchF110Env(num_envs=N, num_agents=1, map=os.path.join(MAPS, "example_map"), dtype="fp32", noise="philox",
+                       auto_reset=True, reset_poses=pool, raycast_variant=2)
+    env.reset(raceline_poses(N)[:, None, :])
+    g = torch.Generator(device="cuda").manual_seed(2024)
+    for t in range(600):
+        act = torch.rand((N, 1, 2), generator=g, device="cuda", dtype=torch.float64)
+        act[..., 0] = (act[..., 0] * 2 - 1) * 0.4189
+        act[..., 1] = act[..., 1] * 8.0
+        obs, rew, done, info = env.step(act)
+    assert int(env.episode_count.max()) >= 2          # crashed envs restarted
+    st = _state(env)
+    assert np.isfinite(st).all() and np.isfinite(obs["scans"].cpu().numpy()).all()
+    # a restarted env sits on a pool pose right after its reset step
+    assert float(obs["scans"].min()) >= -0.1 and float(obs["scans"].max()) <= 30.1
+
+
+def test_step_host_matches_device_step():
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    import torch
+    N = 16384
+    kw = dict(map=os.path.join(MAPS, "example_map"), num_agents=1, num_envs=N, dtype="fp32", noise="philox")
+    a, b = BatchF110Env(**kw), BatchF110Env(**kw)
+    poses = raceline_poses(N)[:, None, :]
+    a.reset(poses); b.reset(poses)
+    act = torch.zeros((N, 1, 2), dtype=torch.float64).pin_memory()
+    obs = torch.zeros((10, N, 1), dtype=torch.float64).pin_memory()
+    scans = torch.zeros((N, 1, 1080), dtype=torch.float32).pin_memory()
+    done = torch.zeros((N,), dtype=torch.uint8).pin_memory()
+    rng = np.random.default_rng(0)
+    for t in range(5):
+        act.numpy()[...] = np.stack([rng.uniform(-0.3, 0.3, (N, 1)), rng.uniform(0.0, 7.0, (N, 1))], axis=-1)
+        a.step(act.numpy())
+        b.step_host(act, obs, scans, done)
+    assert (a.obs_block.cpu() == obs).all()
+    assert (a.scans.cpu() == scans).all()
+    assert (a.done.cpu() == done).all()
