@@ -33,9 +33,11 @@ struct f110_sim {
     F110Dev d;
     std::vector<void *> allocs;
     bool has_map = false, has_tables = false;
-    double *edt64 = nullptr, *edt64_t = nullptr;
-    float *edt32_t = nullptr;
-    float2 *dir32 = nullptr;
+    double *edt64 = nullptr;
+    float *edt32 = nullptr;
+    cudaArray_t edt_arr = nullptr;
+    cudaTextureObject_t edt_tex = 0;
+    float4 *dir32 = nullptr;
     double *noise = nullptr;
     long long noise_cap = 0;
     double *pool = nullptr;
@@ -62,6 +64,17 @@ static int dev_alloc(f110_sim *s, T **p, size_t n, bool zero = true)
     return 0;
 }
 #define TRY(x) do { int r_ = (x); if (r_) return r_; } while (0)
+
+// per-angle ray direction in the map frame and its reciprocals (1/0 stored as -inf, see trace32)
+static void build_dir_table(const double *sines, const double *cosines, int T, double oc, double os, std::vector<float4> &dir)
+{
+    dir.resize(T);
+    for (int i = 0; i < T; i++) {
+        float dx = (float)(cosines[i] * oc + sines[i] * os), dy = (float)(-cosines[i] * os + sines[i] * oc);
+        float ix = dx != 0.f ? 1.0f / dx : -INFINITY, iy = dy != 0.f ? 1.0f / dy : -INFINITY;
+        dir[i] = make_float4(dx, dy, ix, iy);
+    }
+}
 
 extern "C" const char *f110_last_error(void) { return g_err.c_str(); }
 extern "C" int f110_abi_version(void) { return F110_ABI_VERSION; }
@@ -144,8 +157,8 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
         d.sines = tabs; d.cosines = tabs + cfg->theta_dis;
         d.scan_angles = tabs + 2 * cfg->theta_dis; d.beam_cos = d.scan_angles + B; d.side_dist = d.beam_cos + B;
         float *tabs32 = nullptr;
-        if ((rc = dev_alloc(s, &tabs32, 2 * B))) break;
-        d.beam_cos32 = tabs32; d.side_dist32 = tabs32 + B;
+        if ((rc = dev_alloc(s, &tabs32, 3 * B))) break;
+        d.beam_cos32 = tabs32; d.side_dist32 = tabs32 + B; d.ttc_k32 = tabs32 + 2 * B;
         if ((rc = dev_alloc(s, &s->dir32, (size_t)cfg->theta_dis))) break;
         d.dir32 = s->dir32;
         double *params = nullptr;
@@ -178,8 +191,9 @@ extern "C" int f110_destroy(f110_sim *s)
     cudaDeviceSynchronize();
     for (void *p : s->allocs) cudaFree(p);
     if (s->edt64) cudaFree(s->edt64);
-    if (s->edt64_t) cudaFree(s->edt64_t);
-    if (s->edt32_t) cudaFree(s->edt32_t);
+    if (s->edt32) cudaFree(s->edt32);
+    if (s->edt_tex) cudaDestroyTextureObject(s->edt_tex);
+    if (s->edt_arr) cudaFreeArray(s->edt_arr);
     if (s->noise) cudaFree(s->noise);
     if (s->pool) cudaFree(s->pool);
     for (cudaEvent_t ev : s->chunk_ev) cudaEventDestroy(ev);
@@ -197,39 +211,49 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
     cudaStream_t st = (cudaStream_t)stream;
     CK(cudaSetDevice(s->device));
     CK(cudaStreamSynchronize(st));
-    if (s->edt64) { cudaFree(s->edt64); cudaFree(s->edt64_t); cudaFree(s->edt32_t); s->edt64 = nullptr; }
+    if (s->edt64) { cudaFree(s->edt64); cudaFree(s->edt32); s->edt64 = nullptr; s->edt32 = nullptr; }
+    if (s->edt_tex) { cudaDestroyTextureObject(s->edt_tex); s->edt_tex = 0; }
+    if (s->edt_arr) { cudaFreeArray(s->edt_arr); s->edt_arr = nullptr; }
     F110Dev &d = s->d;
     size_t cells = (size_t)h * w;
-    int tx64 = (w + F110_T64_W - 1) / F110_T64_W, ty64 = (h + F110_T64_H - 1) / F110_T64_H;
-    int tx32 = (w + F110_T32_W - 1) / F110_T32_W, ty32 = (h + F110_T32_H - 1) / F110_T32_H;
+    if (cells >= (1ull << 31)) return fail(F110_ERR_INVALID, "map too large");
     CK(cudaMalloc(&s->edt64, cells * 8));
-    CK(cudaMalloc(&s->edt64_t, (size_t)tx64 * ty64 * 16 * 8));
-    CK(cudaMalloc(&s->edt32_t, (size_t)tx32 * ty32 * 32 * 4));
+    CK(cudaMalloc(&s->edt32, cells * 4));
     CK(cudaMemcpyAsync(s->edt64, edt, cells * 8, cudaMemcpyHostToDevice, st));
     d.map_h = h; d.map_w = w; d.res = res; d.inv_res = 1.0 / res; d.ox = ox; d.oy = oy; d.oc = oc; d.os = os;
     d.xmax = w * res; d.ymax = h * res;   // width * resolution, height * resolution (laser_models.py:79)
     int ex;
     d.res_pow2 = (frexp(res, &ex) == 0.5);
     d.has_rot = !(oc == 1.0 && os == 0.0);
-    d.tiles_x64 = tx64; d.tiles_x32 = tx32;
     d.oob64 = edt[cells - 1];             // dt[-1, -1]
-    d.oob32 = (float)(edt[cells - 1] / res);
-    d.edt64 = s->edt64; d.edt64_t = s->edt64_t; d.edt32_t = s->edt32_t;
-    f110_launch_tile64(s->edt64, s->edt64_t, h, w, st);
-    f110_launch_tile32(s->edt64, s->edt32_t, h, w, d.inv_res, st);
-    s->launches += 2;
+    d.oob32 = edt[cells - 1] > s->cfg.eps ? (float)(edt[cells - 1] / res) : 1024.0f;
+    d.edt64 = s->edt64; d.edt32 = s->edt32;
+    f110_launch_edt32(s->edt64, s->edt32, cells, d.inv_res, s->cfg.eps, st);
+    s->launches += 1;
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(st));
+    // the same fp32 map as a CUDA array behind a point-sampled texture (2D-local layout, floor + address in the TEX unit)
+    {
+        cudaChannelFormatDesc fd = cudaCreateChannelDesc<float>();
+        CK(cudaMallocArray(&s->edt_arr, &fd, (size_t)w, (size_t)h));
+        CK(cudaMemcpy2DToArray(s->edt_arr, 0, 0, s->edt32, (size_t)w * 4, (size_t)w * 4, (size_t)h, cudaMemcpyDeviceToDevice));
+        cudaResourceDesc rd; memset(&rd, 0, sizeof(rd));
+        rd.resType = cudaResourceTypeArray; rd.res.array.array = s->edt_arr;
+        cudaTextureDesc td; memset(&td, 0, sizeof(td));
+        td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
+        CK(cudaCreateTextureObject(&s->edt_tex, &rd, &td, nullptr));
+        d.edt_tex = (unsigned long long)s->edt_tex;
+    }
     s->has_map = true;
     // direction table depends on the map rotation: rebuild if tables are already there
     if (s->has_tables) {
         std::vector<double> sn(d.theta_dis), cs(d.theta_dis);
         CK(cudaMemcpy(sn.data(), d.sines, d.theta_dis * 8, cudaMemcpyDeviceToHost));
         CK(cudaMemcpy(cs.data(), d.cosines, d.theta_dis * 8, cudaMemcpyDeviceToHost));
-        std::vector<float2> dir(d.theta_dis);
-        for (int i = 0; i < d.theta_dis; i++)
-            dir[i] = make_float2((float)(cs[i] * oc + sn[i] * os), (float)(-cs[i] * os + sn[i] * oc));
-        CK(cudaMemcpy(s->dir32, dir.data(), dir.size() * sizeof(float2), cudaMemcpyHostToDevice));
+        std::vector<float4> dir;
+        build_dir_table(sn.data(), cs.data(), d.theta_dis, oc, os, dir);
+        CK(cudaMemcpy(s->dir32, dir.data(), dir.size() * sizeof(float4), cudaMemcpyHostToDevice));
     }
     return F110_OK;
 }
@@ -248,14 +272,16 @@ extern "C" int f110_set_tables(f110_sim *s, const double *sines, const double *c
     CK(cudaMemcpy((void *)d.scan_angles, scan_angles, B * 8, cudaMemcpyHostToDevice));
     CK(cudaMemcpy((void *)d.beam_cos, beam_cosines, B * 8, cudaMemcpyHostToDevice));
     CK(cudaMemcpy((void *)d.side_dist, side_distances, B * 8, cudaMemcpyHostToDevice));
-    std::vector<float> f(2 * B);
-    for (int i = 0; i < B; i++) { f[i] = (float)beam_cosines[i]; f[B + i] = (float)side_distances[i]; }
+    std::vector<float> f(3 * B);
+    for (int i = 0; i < B; i++) {
+        f[i] = (float)beam_cosines[i]; f[B + i] = (float)side_distances[i];
+        f[2 * B + i] = (float)(1.2 * s->cfg.ttc_thresh * fabs(beam_cosines[i]));
+    }
     CK(cudaMemcpy((void *)d.beam_cos32, f.data(), f.size() * 4, cudaMemcpyHostToDevice));
     double oc = s->has_map ? d.oc : 1.0, os = s->has_map ? d.os : 0.0;
-    std::vector<float2> dir(T);
-    for (int i = 0; i < T; i++)
-        dir[i] = make_float2((float)(cosines[i] * oc + sines[i] * os), (float)(-cosines[i] * os + sines[i] * oc));
-    CK(cudaMemcpy(s->dir32, dir.data(), dir.size() * sizeof(float2), cudaMemcpyHostToDevice));
+    std::vector<float4> dir;
+    build_dir_table(sines, cosines, T, oc, os, dir);
+    CK(cudaMemcpy(s->dir32, dir.data(), dir.size() * sizeof(float4), cudaMemcpyHostToDevice));
     s->has_tables = true;
     return F110_OK;
 }
@@ -442,6 +468,7 @@ extern "C" int f110_raycast(f110_sim *s, const double *poses_dev, int32_t n, voi
     if (!s) return fail(F110_ERR_INVALID, "null handle");
     if (!s->has_map) return fail(F110_ERR_STATE, "Map is not set for scan simulator.");
     if (!s->has_tables) return fail(F110_ERR_STATE, "scan tables are not set");
+    if (n == 0) return F110_OK;
     if (!poses_dev || !out_dev || n < 0) return fail(F110_ERR_INVALID, "bad raycast arguments");
     CK(cudaSetDevice(s->device));
     if (s->d.scan_is_f32) f110_launch_scan_only32(s->d, poses_dev, n, (float *)out_dev, s->cfg.raycast_variant, (cudaStream_t)stream);

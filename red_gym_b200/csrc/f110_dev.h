@@ -8,13 +8,6 @@ enum { F110_P_MU, F110_P_CSF, F110_P_CSR, F110_P_LF, F110_P_LR, F110_P_H, F110_P
        F110_P_SMAX, F110_P_SVMIN, F110_P_SVMAX, F110_P_VSWITCH, F110_P_AMAX, F110_P_VMIN, F110_P_VMAX,
        F110_P_WIDTH, F110_P_LENGTH, F110_NP };
 
-// EDT tile for the tiled layouts: a 128-byte line holds a 2D patch instead of a row strip.
-//   fp64: 4 x 4 cells,  fp32: 8 x 4 cells (x fastest inside the tile)
-#define F110_T64_W 4
-#define F110_T64_H 4
-#define F110_T32_W 8
-#define F110_T32_H 4
-
 struct F110Dev {
     int n_envs, n_agents, n_beams, integrator, ego_idx, theta_dis;
     int noise_mode, auto_reset, count_lookups, n_pool, scan_is_f32;
@@ -22,18 +15,17 @@ struct F110Dev {
     unsigned long long seed;
     // map
     int map_h, map_w, res_pow2, has_rot;
-    int tiles_x64, tiles_x32;          // tiles per row of the tiled layouts
     double res, inv_res, ox, oy, oc, os, xmax, ymax;
     double oob64;                      // dt[-1,-1] : value an out-of-map lookup returns
     float oob32;
-    const double *edt64;               // row-major [h][w]
-    const double *edt64_t;             // tiled
-    const float *edt32_t;              // tiled, in CELL units (metres / res)
+    const double *edt64;               // row-major [h][w], metres
+    const float *edt32;                // row-major [h][w], in CELL units (metres / res); obstacle cells hold 1024 (see fp32 kernels)
+    unsigned long long edt_tex;        // cudaTextureObject_t over a CUDA array with the same content (point sampling)
     // tables
     const double *sines, *cosines;                  // theta_dis
     const double *scan_angles, *beam_cos, *side_dist;  // n_beams
-    const float2 *dir32;                            // theta_dis: ray direction in cell units per unit cell length
-    const float *beam_cos32, *side_dist32;
+    const float4 *dir32;                            // theta_dis: (dx, dy, 1/dx, 1/dy), unit ray direction in the map frame
+    const float *beam_cos32, *side_dist32, *ttc_k32; // n_beams; ttc_k = 1.2 * ttc_thresh * |cos|
     const double *params;                           // (n_agents + 1) * F110_NP
     // per (env, agent)
     double *state;       // [7][NA]
@@ -70,5 +62,4 @@ void f110_launch_finalize(const F110Dev &d, cudaStream_t st);    // collisions, 
 void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, double *out, int variant, cudaStream_t st);
 void f110_launch_scan_only32(const F110Dev &d, const double *poses, int n, float *out, int variant, cudaStream_t st);
 void f110_launch_reset(const F110Dev &d, const double *poses_dev, const double *rot_dev, const uint8_t *mask_dev, cudaStream_t st);
-void f110_launch_tile64(const double *src, double *dst, int h, int w, cudaStream_t st);
-void f110_launch_tile32(const double *src, float *dst, int h, int w, double inv_res, cudaStream_t st);
+void f110_launch_edt32(const double *src, float *dst, size_t cells, double inv_res, double eps, cudaStream_t st);

@@ -189,7 +189,7 @@ void f110_launch_dynamics(const F110Dev &d, cudaStream_t st)
 }
 
 // ------------------------------------------------------------------------------------------------
-// lidar: sphere tracing against the EDT (laser_models.py:56-186)
+// lidar: sphere tracing against the EDT (laser_models.py:56-186), fp64 parity path
 // ------------------------------------------------------------------------------------------------
 // Truncation of a non-negative double < 2^31 without the (quarter-rate) F2I.F64 path: adding 2^52
 // with round-toward-zero leaves floor(q) in the low mantissa word.  `whole` gets floor(q) as a double.
@@ -207,17 +207,18 @@ static __device__ __forceinline__ int trunc_nonneg(double q, double &whole)
 template <bool POW2>
 static __device__ __forceinline__ int cell_index(double v, const F110Dev &d)
 {
-    double q = v * d.inv_res, whole;
+    double q = v * d.inv_res;
+    if (POW2) return __double2loint(__dadd_rz(q, 4503599627370496.0));
+    double whole;
     int c = trunc_nonneg(q, whole);
-    if (!POW2) {
-        double frac = q - whole;
-        if (frac < 1e-9 || frac > 1.0 - 1e-9) c = (int)__ddiv_rn(v, d.res);
-    }
+    double frac = q - whole;
+    if (frac < 1e-9 || frac > 1.0 - 1e-9) c = (int)__ddiv_rn(v, d.res);
     return c;
 }
 
-// distance_transform(x, y) (laser_models.py:89-104): out of bounds -> (-1,-1) -> last cell.
-template <bool ROT, bool POW2, bool TILED>
+// distance_transform(x, y) (laser_models.py:89-104).  CHECKED: with the bounds test of xy_2_rc
+// (out of bounds -> (-1,-1) -> last cell); unchecked: caller proved the point is inside the map.
+template <bool ROT, bool POW2, bool CHECKED>
 static __device__ __forceinline__ double edt_lookup(const F110Dev &d, double x, double y)
 {
     double xt = x - d.ox, yt = y - d.oy;
@@ -228,14 +229,12 @@ static __device__ __forceinline__ double edt_lookup(const F110Dev &d, double x, 
     } else {   // origin yaw == 0: x*1 + y*0 is x (bit-exact for finite inputs)
         xr = xt; yr = yt;
     }
-    if (xr < 0 || xr >= d.xmax || yr < 0 || yr >= d.ymax) return d.oob64;
+    if (CHECKED) {
+        if (xr < 0 || xr >= d.xmax || yr < 0 || yr >= d.ymax) return d.oob64;
+    }
     int c = cell_index<POW2>(xr, d);
     int r = cell_index<POW2>(yr, d);
-    if (TILED) {
-        unsigned idx = (((unsigned)(r >> 2) * d.tiles_x64 + (unsigned)(c >> 2)) << 4) | ((r & 3) << 2) | (c & 3);
-        return __ldg(d.edt64_t + idx);
-    }
-    return __ldg(d.edt64 + (size_t)r * d.map_w + c);
+    return __ldg(d.edt64 + ((unsigned)r * (unsigned)d.map_w + (unsigned)c));
 }
 
 // Start of the float beam index of get_scan (laser_models.py:166-172)
@@ -271,18 +270,53 @@ static __device__ __forceinline__ int theta_index_of(const F110Dev &d, double t0
     return k;
 }
 
-// trace_ray (laser_models.py:107-146) given the first lookup d0 at the scan origin
-template <bool ROT, bool POW2, bool TILED>
-static __device__ __forceinline__ double trace_ray(const F110Dev &d, double x, double y, double cs, double sn,
-                                                   double d0, unsigned &nlook)
+// Per-scan data for hoisting the bounds test out of the loop: distances (metres, map frame) from the
+// scan origin to the map border minus a 2-cell margin.  While the accumulated range of a ray is below
+// the range at which it crosses that margin, every lookup is inside the map and the test of
+// xy_2_rc (:79) is provably false -- skipping it changes no result.
+struct Scan64 {
+    double px, py, d0, t0;
+    float x_lo, x_hi, y_lo, y_hi, max_fast;
+};
+
+template <bool ROT>
+static __device__ __forceinline__ void scan_setup64(const F110Dev &d, double px, double py, double yaw, Scan64 &c)
 {
-    double dist = d0, total = d0;
+    c.px = px; c.py = py;
+    c.t0 = theta_start(d, yaw);
+    double xt = px - d.ox, yt = py - d.oy;
+    double xr = ROT ? xt * d.oc + yt * d.os : xt;
+    double yr = ROT ? -xt * d.os + yt * d.oc : yt;
+    float margin = 2.0f * (float)d.res;
+    c.x_lo = margin - (float)xr; c.x_hi = (float)d.xmax - margin - (float)xr;
+    c.y_lo = margin - (float)yr; c.y_hi = (float)d.ymax - margin - (float)yr;
+    c.max_fast = (c.x_lo <= 0.f && c.x_hi >= 0.f && c.y_lo <= 0.f && c.y_hi >= 0.f) ? (float)d.max_range : -1.0f;
+}
+
+// trace_ray (laser_models.py:107-146) given the first lookup d0 at the scan origin
+template <bool ROT, bool POW2, bool COUNT>
+static __device__ __forceinline__ double trace_ray(const F110Dev &d, const Scan64 &c, int ti, unsigned &nlook)
+{
+    const double sn = __ldg(d.sines + ti), cs = __ldg(d.cosines + ti);
+    // fp32 estimate (conservative through the margin) of the range where the ray nears the border
+    const float4 dir = __ldg(d.dir32 + ti);
+    float tx = (dir.x > 0.f ? c.x_hi : c.x_lo) * dir.z;
+    float ty = (dir.y > 0.f ? c.y_hi : c.y_lo) * dir.w;
+    const double t_fast = (double)fminf(fminf(tx, ty), c.max_fast);
+    double x = c.px, y = c.py, dist = c.d0, total = c.d0;
+    while (dist > d.eps && total <= t_fast) {
+        x += dist * cs;
+        y += dist * sn;
+        dist = edt_lookup<ROT, POW2, false>(d, x, y);
+        total += dist;
+        if (COUNT) nlook++;
+    }
     while (dist > d.eps && total <= d.max_range) {
         x += dist * cs;
         y += dist * sn;
-        dist = edt_lookup<ROT, POW2, TILED>(d, x, y);
+        dist = edt_lookup<ROT, POW2, true>(d, x, y);
         total += dist;
-        nlook++;
+        if (COUNT) nlook++;
     }
     if (total > d.max_range) total = d.max_range;
     return total;
@@ -302,21 +336,21 @@ static __device__ __forceinline__ bool ttc_hit(double range, double side, double
 // One warp per scan, 32 consecutive beams in lockstep per round (adjacent beams hit adjacent EDT
 // cells, so a warp-level gather touches few cache lines); lanes whose ray has converged idle until
 // the round's slowest ray is done.
-template <bool ROT, bool POW2, bool TILED, bool STEP>
+template <bool ROT, bool POW2, bool STEP, bool COUNT>
 static __device__ __forceinline__ void scan_rounds(const F110Dev &d, double px, double py, double yaw,
                                                    double *__restrict__ out, const double *__restrict__ noise_row,
                                                    double vel, bool &hit_any, unsigned &nlook)
 {
     const int lane = threadIdx.x & 31;
-    const double t0 = theta_start(d, yaw);
-    const double d0 = edt_lookup<ROT, POW2, TILED>(d, px, py);
-    nlook += (lane == 0);
+    Scan64 c;
+    scan_setup64<ROT>(d, px, py, yaw, c);
+    c.d0 = edt_lookup<ROT, POW2, true>(d, px, py);
+    if (COUNT) nlook += (lane == 0);
     for (int base = 0; base < d.n_beams; base += 32) {
         int i = base + lane;
         if (i < d.n_beams) {
-            int ti = theta_index_of(d, t0, i);
-            double sn = __ldg(d.sines + ti), cs = __ldg(d.cosines + ti);
-            double r = trace_ray<ROT, POW2, TILED>(d, px, py, cs, sn, d0, nlook);
+            int ti = theta_index_of(d, c.t0, i);
+            double r = trace_ray<ROT, POW2, COUNT>(d, c, ti, nlook);
             if (noise_row) r += __ldg(noise_row + i);
             out[i] = r;
             if (STEP && vel != 0.0)
@@ -325,7 +359,7 @@ static __device__ __forceinline__ void scan_rounds(const F110Dev &d, double px, 
     }
 }
 
-template <bool ROT, bool POW2, bool TILED>
+template <bool ROT, bool POW2, bool COUNT>
 __global__ void __launch_bounds__(256) k_raycast64(const F110Dev d, int env_begin, int env_count)
 {
     const int NA = d.n_envs * d.n_agents;
@@ -345,7 +379,7 @@ __global__ void __launch_bounds__(256) k_raycast64(const F110Dev d, int env_begi
     }
     bool hit = false;
     unsigned nlook = 0;
-    scan_rounds<ROT, POW2, TILED, true>(d, px, py, yaw, (double *)d.scans + (size_t)ia * d.n_beams, noise_row, vel, hit, nlook);
+    scan_rounds<ROT, POW2, true, COUNT>(d, px, py, yaw, (double *)d.scans + (size_t)ia * d.n_beams, noise_row, vel, hit, nlook);
     hit = __any_sync(FULL, hit);
     // RaceCar.check_ttc (base_classes.py:241-250): state[3:] = 0 -- velocity, YAW, yaw rate, slip
     if (lane == 0) {
@@ -355,14 +389,14 @@ __global__ void __launch_bounds__(256) k_raycast64(const F110Dev d, int env_begi
         }
         d.in_collision[ia] = hit ? 1 : 0;
     }
-    if (d.count_lookups) {
+    if (COUNT) {
 #pragma unroll
         for (int o = 16; o; o >>= 1) nlook += __shfl_xor_sync(FULL, nlook, o);
         if (lane == 0) atomicAdd(d.lookups, (unsigned long long)nlook);
     }
 }
 
-template <bool ROT, bool POW2, bool TILED>
+template <bool ROT, bool POW2, bool COUNT>
 __global__ void __launch_bounds__(256) k_scan_only64(const F110Dev d, const double *__restrict__ poses, int n,
                                                      double *__restrict__ out)
 {
@@ -370,9 +404,9 @@ __global__ void __launch_bounds__(256) k_scan_only64(const F110Dev d, const doub
     if (w >= n) return;
     bool hit = false;
     unsigned nlook = 0;
-    scan_rounds<ROT, POW2, TILED, false>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], out + (size_t)w * d.n_beams,
+    scan_rounds<ROT, POW2, false, COUNT>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], out + (size_t)w * d.n_beams,
                                          nullptr, 0.0, hit, nlook);
-    if (d.count_lookups) {
+    if (COUNT) {
 #pragma unroll
         for (int o = 16; o; o >>= 1) nlook += __shfl_xor_sync(FULL, nlook, o);
         if ((threadIdx.x & 31) == 0) atomicAdd(d.lookups, (unsigned long long)nlook);
@@ -381,15 +415,15 @@ __global__ void __launch_bounds__(256) k_scan_only64(const F110Dev d, const doub
 
 #define DISPATCH64(KERNEL, GRID, ...)                                                             \
     do {                                                                                          \
-        bool tiled = (variant & 1) != 0;                                                          \
+        bool cnt = d.count_lookups != 0;                                                          \
         if (d.has_rot) {                                                                          \
-            if (tiled) KERNEL<true, false, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);              \
+            if (cnt) KERNEL<true, false, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);                \
             else KERNEL<true, false, false><<<GRID, 256, 0, st>>>(__VA_ARGS__);                   \
         } else if (d.res_pow2) {                                                                  \
-            if (tiled) KERNEL<false, true, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);              \
+            if (cnt) KERNEL<false, true, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);                \
             else KERNEL<false, true, false><<<GRID, 256, 0, st>>>(__VA_ARGS__);                   \
         } else {                                                                                  \
-            if (tiled) KERNEL<false, false, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);             \
+            if (cnt) KERNEL<false, false, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);               \
             else KERNEL<false, false, false><<<GRID, 256, 0, st>>>(__VA_ARGS__);                  \
         }                                                                                         \
     } while (0)
@@ -728,38 +762,17 @@ void f110_launch_reset(const F110Dev &d, const double *poses_dev, const double *
 }
 
 // ------------------------------------------------------------------------------------------------
-// EDT re-layout: row-major fp64 -> 2D tiles so that one 128-byte line is a 4x4 (fp64) / 8x4 (fp32)
-// patch of cells; the fp32 copy is stored in CELL units (metres / resolution).
+// fp32 copy of the EDT in CELL units (metres / resolution) for the fast path
 // ------------------------------------------------------------------------------------------------
-__global__ void k_tile64(const double *__restrict__ src, double *__restrict__ dst, int h, int w, int tiles_x)
+__global__ void k_edt32(const double *__restrict__ src, float *__restrict__ dst, size_t cells, double inv_res, double eps)
 {
-    int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y * blockDim.y + threadIdx.y;
-    int wp = tiles_x * F110_T64_W;
-    int hp = ((h + F110_T64_H - 1) / F110_T64_H) * F110_T64_H;
-    if (c >= wp || r >= hp) return;
-    double v = (c < w && r < h) ? src[(size_t)r * w + c] : 0.0;
-    size_t idx = (((size_t)(r >> 2) * tiles_x + (c >> 2)) << 4) | ((r & 3) << 2) | (c & 3);
-    dst[idx] = v;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < cells) {
+        double v = src[i];
+        dst[i] = (v > eps) ? (float)(v * inv_res) : 1024.0f;   // trace_ray stops when dist <= eps: sentinel (fp32 kernels)
+    }
 }
-__global__ void k_tile32(const double *__restrict__ src, float *__restrict__ dst, int h, int w, int tiles_x, double inv_res)
+void f110_launch_edt32(const double *src, float *dst, size_t cells, double inv_res, double eps, cudaStream_t st)
 {
-    int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y * blockDim.y + threadIdx.y;
-    int wp = tiles_x * F110_T32_W;
-    int hp = ((h + F110_T32_H - 1) / F110_T32_H) * F110_T32_H;
-    if (c >= wp || r >= hp) return;
-    double v = (c < w && r < h) ? src[(size_t)r * w + c] * inv_res : 0.0;
-    size_t idx = (((size_t)(r >> 2) * tiles_x + (c >> 3)) << 5) | ((r & 3) << 3) | (c & 7);
-    dst[idx] = (float)v;
-}
-void f110_launch_tile64(const double *src, double *dst, int h, int w, cudaStream_t st)
-{
-    int tiles_x = (w + F110_T64_W - 1) / F110_T64_W;
-    dim3 b(32, 8), g((tiles_x * F110_T64_W + 31) / 32, (h + F110_T64_H + 7) / 8);
-    k_tile64<<<g, b, 0, st>>>(src, dst, h, w, tiles_x);
-}
-void f110_launch_tile32(const double *src, float *dst, int h, int w, double inv_res, cudaStream_t st)
-{
-    int tiles_x = (w + F110_T32_W - 1) / F110_T32_W;
-    dim3 b(32, 8), g((tiles_x * F110_T32_W + 31) / 32, (h + F110_T32_H + 7) / 8);
-    k_tile32<<<g, b, 0, st>>>(src, dst, h, w, tiles_x, inv_res);
+    k_edt32<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(src, dst, cells, inv_res, eps);
 }
