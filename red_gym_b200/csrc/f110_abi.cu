@@ -117,6 +117,7 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
     d.scan_is_f32 = cfg->precision == F110_PRECISION_FP32;
     d.timestep = cfg->timestep; d.fov = cfg->fov; d.eps = cfg->eps; d.max_range = cfg->max_range;
     d.ttc_thresh = cfg->ttc_thresh; d.noise_std = cfg->noise_std; d.seed = cfg->seed;
+    d.noise_std32 = (float)cfg->noise_std; d.ttc_thresh32 = (float)cfg->ttc_thresh;
     // laser_models.py:367-368
     double angle_increment = cfg->fov / (cfg->n_beams - 1);
     d.theta_inc = cfg->theta_dis * angle_increment / (2. * M_PI);
@@ -225,6 +226,7 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
     int ex;
     d.res_pow2 = (frexp(res, &ex) == 0.5);
     d.has_rot = !(oc == 1.0 && os == 0.0);
+    d.max_c32 = (float)(s->cfg.max_range / res); d.res32 = (float)res;
     d.oob64 = edt[cells - 1];             // dt[-1, -1]
     d.oob32 = edt[cells - 1] > s->cfg.eps ? (float)(edt[cells - 1] / res) : 1024.0f;
     d.edt64 = s->edt64; d.edt32 = s->edt32;
@@ -273,10 +275,13 @@ extern "C" int f110_set_tables(f110_sim *s, const double *sines, const double *c
     CK(cudaMemcpy((void *)d.beam_cos, beam_cosines, B * 8, cudaMemcpyHostToDevice));
     CK(cudaMemcpy((void *)d.side_dist, side_distances, B * 8, cudaMemcpyHostToDevice));
     std::vector<float> f(3 * B);
+    float side_max = 0.f;
     for (int i = 0; i < B; i++) {
         f[i] = (float)beam_cosines[i]; f[B + i] = (float)side_distances[i];
         f[2 * B + i] = (float)(1.2 * s->cfg.ttc_thresh * fabs(beam_cosines[i]));
+        if (side_distances[i] < 1e30 && (float)side_distances[i] > side_max) side_max = (float)side_distances[i];
     }
+    d.side_max32 = side_max;
     CK(cudaMemcpy((void *)d.beam_cos32, f.data(), f.size() * 4, cudaMemcpyHostToDevice));
     double oc = s->has_map ? d.oc : 1.0, os = s->has_map ? d.os : 0.0;
     std::vector<float4> dir;

@@ -13,6 +13,7 @@ struct F110Dev {
     int noise_mode, auto_reset, count_lookups, n_pool, scan_is_f32;
     double timestep, fov, eps, max_range, theta_inc, ttc_thresh, noise_std;
     unsigned long long seed;
+    float max_c32, res32, noise_std32, ttc_thresh32, side_max32;   // fp32 path constants (cells / metres)
     // map
     int map_h, map_w, res_pow2, has_rot;
     double res, inv_res, ox, oy, oc, os, xmax, ymax;
