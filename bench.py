@@ -165,7 +165,7 @@ def run_b200(args):
     B = 1080
     env = BatchF110Env(num_envs=n_envs, device=local, dtype=dtype, noise=noise, num_agents=agents, auto_reset=True,
                        reset_poses=make_poses(1024, agents), raycast_variant=args.variant,
-                       map=os.path.join(MAPS_DIR, "example_map"), seed=12345 + rank)
+                       map=os.path.join(MAPS_DIR, "example_map"), seed=12345, env_offset=rank * n_envs)
     # every workload auto-resets here: a throughput run must keep cars alive (the parity tests cover no-reset runs)
     env.reset(make_poses(n_envs, agents))
     bank = action_bank(torch, n_envs, agents, device, 8, 2024 + rank)
@@ -225,7 +225,9 @@ def run_b200(args):
     traffic = None
     tp = os.path.join(REPO, "profiles", "roofline_traffic.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get(args.workload)
+        t_ = json.load(open(tp)).get(dtype)
+        if t_:   # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture, scaled to this launch's scan count
+            traffic = t_["dram_bytes_per_scan"] * n_envs * agents
     roofline = {"kernel": "k_raycast32" if dtype == "fp32" else "k_raycast64", "bound": "hbm", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "launch_ms": rc_avg_ms, "lookups_per_scan": lookups_per_scan, "kernel_lookups_per_scan": kernel_lookups_per_scan, "bytes_per_scan": bytes_per_scan,

@@ -69,7 +69,8 @@ typedef struct f110_config {
     int32_t auto_reset;       /* 0: like the reference (keep stepping after done); 1: a done env restarts from
                                  the reset-pose pool on its next step (that step IS the reset's zero-action step) */
     int32_t raycast_variant;  /* 0 = default; >0 selects an experimental kernel variant (bench only) */
-    int32_t reserved0;
+    int32_t env_offset;       /* global id of this handle's env 0 (env sharding): keys the Philox noise and the reset-pool
+                                 choice, so per-env results do not depend on how envs are split over GPUs */
     double timestep;          /* f110_env.py:137 */
     double fov;               /* f110_env.py:154-157 */
     double eps;               /* 1e-4  (laser_models.py:360) */
@@ -98,6 +99,7 @@ typedef struct f110_buffers {
     double *actions;        /* [N][A][2] device staging for f110_step_host (may also be written by the caller) */
     int64_t *episode_count; /* [N] number of (auto-)resets */
     uint64_t *lookups;      /* [1] EDT lookups counted when count_lookups was enabled */
+    uint8_t *checkpoint_done; /* [N][A] toggle_list >= 4 (info['checkpoint_done'], f110_env.py:244,300) */
 } f110_buffers;
 
 const char *f110_last_error(void);

@@ -29,7 +29,7 @@ class Config(ctypes.Structure):
     _fields_ = [("abi_version", ctypes.c_int32), ("n_envs", ctypes.c_int32), ("n_agents", ctypes.c_int32),
                 ("n_beams", ctypes.c_int32), ("integrator", ctypes.c_int32), ("ego_idx", ctypes.c_int32),
                 ("theta_dis", ctypes.c_int32), ("precision", ctypes.c_int32), ("noise_mode", ctypes.c_int32),
-                ("auto_reset", ctypes.c_int32), ("raycast_variant", ctypes.c_int32), ("reserved0", ctypes.c_int32),
+                ("auto_reset", ctypes.c_int32), ("raycast_variant", ctypes.c_int32), ("env_offset", ctypes.c_int32),
                 ("timestep", ctypes.c_double), ("fov", ctypes.c_double), ("eps", ctypes.c_double),
                 ("max_range", ctypes.c_double), ("ttc_thresh", ctypes.c_double), ("noise_std", ctypes.c_double),
                 ("seed", ctypes.c_uint64)]
@@ -38,7 +38,7 @@ class Config(ctypes.Structure):
 class Buffers(ctypes.Structure):
     _fields_ = [(n, ctypes.c_void_p) for n in
                 ("state", "obs_block", "collisions", "collision_idx", "lap_times", "lap_counts", "toggles", "done",
-                 "in_collision", "scans", "cur_time", "noise_step", "actions", "episode_count", "lookups")]
+                 "in_collision", "scans", "cur_time", "noise_step", "actions", "episode_count", "lookups", "checkpoint_done")]
 
 
 _lib = None

@@ -34,11 +34,11 @@ class BatchF110Env(object):
         ego_idx, integrator, fov.
     Batch kwargs: num_envs; device (CUDA ordinal); dtype 'fp64' (parity path) | 'fp32' (fast lidar);
         noise 'numpy' (host PCG64 rows, parity) | 'philox' (device) | 'off'; num_beams (1080);
-        auto_reset + reset_poses (pool [P, A, 3]) for throughput runs.
+        auto_reset + reset_poses (pool [P, A, 3]) for throughput runs; env_offset = global id of env 0 (sharding).
     """
 
     def __init__(self, num_envs=1, device=0, dtype="fp64", noise=None, num_beams=1080, auto_reset=False,
-                 reset_poses=None, raycast_variant=0, map_data=None, **kwargs):
+                 reset_poses=None, raycast_variant=0, map_data=None, env_offset=0, **kwargs):
         import torch
         self._torch = torch
         self.lib = nat.load()
@@ -65,7 +65,7 @@ class BatchF110Env(object):
         cfg = nat.Config(abi_version=nat.F110_ABI_VERSION, n_envs=self.num_envs, n_agents=self.num_agents,
                          n_beams=self.num_beams, integrator=_integrator_code(self.integrator), ego_idx=self.ego_idx,
                          theta_dis=2000, precision=nat.PRECISION_FP64 if dtype == "fp64" else nat.PRECISION_FP32,
-                         noise_mode=noise_mode, auto_reset=1 if auto_reset else 0, raycast_variant=raycast_variant,
+                         noise_mode=noise_mode, auto_reset=1 if auto_reset else 0, raycast_variant=raycast_variant, env_offset=int(env_offset),
                          timestep=self.timestep, fov=self.fov, eps=1e-4, max_range=30.0, ttc_thresh=0.005,
                          noise_std=0.01, seed=self.seed)
         h = ctypes.c_void_p()
@@ -135,6 +135,9 @@ class BatchF110Env(object):
         self.actions = t(b.actions, (N, A, 2), "<f8")
         self.episode_count = t(b.episode_count, (N,), "<i8")
         self._lookups = t(b.lookups, (1,), "<i8")
+        # bool views of the byte flags: step() then launches no torch kernel at all
+        self.checkpoint_done = t(b.checkpoint_done, (N, A), "|u1").view(torch.bool)
+        self.done_bool = self.done.view(torch.bool)
         self._zeros_na = torch.zeros((N, A), dtype=torch.float64, device=self.device)
 
     def set_reset_pool(self, poses):
@@ -199,8 +202,8 @@ class BatchF110Env(object):
                "linear_vels_x": s[3], "linear_vels_y": self._zeros_na, "ang_vels_z": s[5],
                "collisions": self.collisions, "lap_times": self.lap_times, "lap_counts": self.lap_counts}
         reward = self.timestep
-        info = {"checkpoint_done": self.toggle_list >= 4}
-        return obs, reward, self.done.bool(), info
+        info = {"checkpoint_done": self.checkpoint_done}
+        return obs, reward, self.done_bool, info
 
     def step_host(self, actions, obs_block_out, scans_out=None, done_out=None):
         """One step through f110_step_host: host actions in, host observation out (pinned numpy/torch buffers)."""

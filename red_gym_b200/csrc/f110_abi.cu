@@ -115,6 +115,7 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
     d.n_envs = cfg->n_envs; d.n_agents = cfg->n_agents; d.n_beams = cfg->n_beams; d.integrator = cfg->integrator;
     d.ego_idx = cfg->ego_idx; d.theta_dis = cfg->theta_dis; d.noise_mode = cfg->noise_mode; d.auto_reset = cfg->auto_reset;
     d.scan_is_f32 = cfg->precision == F110_PRECISION_FP32;
+    d.env_offset = cfg->env_offset;
     d.timestep = cfg->timestep; d.fov = cfg->fov; d.eps = cfg->eps; d.max_range = cfg->max_range;
     d.ttc_thresh = cfg->ttc_thresh; d.noise_std = cfg->noise_std; d.seed = cfg->seed;
     d.noise_std32 = (float)cfg->noise_std; d.ttc_thresh32 = (float)cfg->ttc_thresh;
@@ -136,6 +137,7 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
         if ((rc = dev_alloc(s, &d.collision_idx, NA))) break;
         if ((rc = dev_alloc(s, &d.toggles, NA))) break;
         if ((rc = dev_alloc(s, &d.near_start, NA))) break;
+        if ((rc = dev_alloc(s, &d.checkpoint_done, NA))) break;
         if ((rc = dev_alloc(s, &d.start_x, NA))) break;
         if ((rc = dev_alloc(s, &d.start_y, NA))) break;
         if ((rc = dev_alloc(s, &d.start_rot, 4 * N))) break;
@@ -490,7 +492,7 @@ extern "C" int f110_get_buffers(f110_sim *s, f110_buffers *o)
     o->state = d.state; o->obs_block = s->obs_block; o->collisions = d.collisions; o->collision_idx = d.collision_idx;
     o->lap_times = d.lap_times; o->lap_counts = d.lap_counts; o->toggles = d.toggles; o->done = d.done;
     o->in_collision = d.in_collision; o->scans = d.scans; o->cur_time = d.cur_time; o->noise_step = (int64_t *)d.noise_step;
-    o->actions = s->actions; o->episode_count = (int64_t *)d.episode_count; o->lookups = (uint64_t *)d.lookups;
+    o->actions = s->actions; o->episode_count = (int64_t *)d.episode_count; o->lookups = (uint64_t *)d.lookups; o->checkpoint_done = d.checkpoint_done;
     return F110_OK;
 }
 

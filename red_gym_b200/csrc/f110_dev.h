@@ -10,7 +10,7 @@ enum { F110_P_MU, F110_P_CSF, F110_P_CSR, F110_P_LF, F110_P_LR, F110_P_H, F110_P
 
 struct F110Dev {
     int n_envs, n_agents, n_beams, integrator, ego_idx, theta_dis;
-    int noise_mode, auto_reset, count_lookups, n_pool, scan_is_f32;
+    int noise_mode, auto_reset, count_lookups, n_pool, scan_is_f32, env_offset;
     double timestep, fov, eps, max_range, theta_inc, ttc_thresh, noise_std;
     unsigned long long seed;
     float max_c32, res32, noise_std32, ttc_thresh32, side_max32;   // fp32 path constants (cells / metres)
@@ -38,6 +38,7 @@ struct F110Dev {
     double *collisions, *collision_idx, *lap_times, *lap_counts;
     int *toggles;
     uint8_t *near_start;
+    uint8_t *checkpoint_done;
     double *start_x, *start_y;
     // per env
     double *start_rot;   // [N][4]

@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(128) k_dynamics(const F110Dev d)
     if (d.auto_reset && d.reset_pending[e]) {
         // F110Env.reset on the device: the pending env restarts from a pool pose and this step is
         // the reset's zero-action step (f110_env.py:318-336)
-        unsigned k = pool_index(e, d.episode_count[e], d.n_pool);
+        unsigned k = pool_index(e + d.env_offset, d.episode_count[e], d.n_pool);
         const double *pp = d.pool + ((size_t)k * d.n_agents + a) * 3;
         x[0] = pp[0]; x[1] = pp[1]; x[2] = 0.; x[3] = 0.; x[4] = pp[2]; x[5] = 0.; x[6] = 0.;
         raw_steer = 0.; vel_cmd = 0.; slen = 0;
@@ -712,6 +712,7 @@ __global__ void __launch_bounds__(128) k_finalize(const F110Dev d)
         else if (!closes && near) { near = false; tg += 1; }
         d.near_start[ia] = near ? 1 : 0;
         d.toggles[ia] = tg;
+        d.checkpoint_done[ia] = tg >= 4 ? 1 : 0;
         d.lap_counts[ia] = (double)(tg / 2);
         if (tg < 4) d.lap_times[ia] = t;
         if (tg < 4) all_done = false;
@@ -754,6 +755,7 @@ __global__ void __launch_bounds__(128) k_reset(const F110Dev d, const double *__
     d.collisions[ia] = 0.;
     d.near_start[ia] = 1;
     d.toggles[ia] = 0;
+    d.checkpoint_done[ia] = 0;
     d.start_x[ia] = p[0];
     d.start_y[ia] = p[1];
     if (a == 0) {

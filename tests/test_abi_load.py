@@ -26,7 +26,7 @@ def test_config_struct_matches_header_layout():
     from red_gym_b200 import _native as nat
     # 12 int32 + 6 double + 1 uint64
     assert ctypes.sizeof(nat.Config) == 12 * 4 + 6 * 8 + 8
-    assert ctypes.sizeof(nat.Buffers) == 15 * ctypes.sizeof(ctypes.c_void_p)
+    assert ctypes.sizeof(nat.Buffers) == 16 * ctypes.sizeof(ctypes.c_void_p)
 
 
 def test_invalid_arguments_are_rejected_before_touching_cuda():

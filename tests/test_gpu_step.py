@@ -191,3 +191,38 @@ def test_step_host_matches_device_step():
     assert (a.obs_block.cpu() == obs).all()
     assert (a.scans.cpu() == scans).all()
     assert (a.done.cpu() == done).all()
+
+
+def test_sharded_run_is_bit_identical_to_unsharded():
+    """envs are independent, so splitting N envs over G handles (GPUs) must not change any per-env result --
+    including the Philox noise stream and the auto-reset pose choice, both keyed by the GLOBAL env id (env_offset)."""
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    from red_gym_b200.sharding import shard_range
+    import torch
+    N, T = 3000, 400
+    pool = raceline_poses(256)[:, None, :]
+    poses = raceline_poses(N)[:, None, :]
+    kw = dict(num_agents=1, map=os.path.join(MAPS, "example_map"), dtype="fp32", noise="philox", auto_reset=True, reset_poses=pool)
+    whole = BatchF110Env(num_envs=N, **kw)
+    shards = []
+    for r in range(3):
+        b, c = shard_range(N, r, 3)
+        shards.append((b, c, BatchF110Env(num_envs=c, env_offset=b, **kw)))
+    whole.reset(poses)
+    for b, c, e in shards:
+        e.reset(poses[b:b + c])
+    g = torch.Generator(device="cuda").manual_seed(7)
+    for t in range(T):
+        act = torch.rand((N, 1, 2), generator=g, device="cuda", dtype=torch.float64)
+        act[..., 0] = (act[..., 0] * 2 - 1) * 0.4189
+        act[..., 1] = act[..., 1] * 8.0
+        whole.step(act)
+        for b, c, e in shards:
+            e.step(act[b:b + c].contiguous())
+    assert int(whole.episode_count.max()) >= 2
+    for b, c, e in shards:
+        assert (e.obs_block == whole.obs_block[:, b:b + c]).all()
+        assert (e.scans == whole.scans[b:b + c]).all()
+        assert (e.episode_count == whole.episode_count[b:b + c]).all()
+        assert (e.toggle_list == whole.toggle_list[b:b + c]).all()
