@@ -34,7 +34,8 @@ struct f110_sim {
     std::vector<void *> allocs;
     bool has_map = false, has_tables = false;
     double *edt64 = nullptr;
-    float *edt32 = nullptr;
+    float *edt32 = nullptr, *edt32p = nullptr;
+    float2 *dir2 = nullptr;
     cudaArray_t edt_arr = nullptr;
     cudaTextureObject_t edt_tex = 0;
     float4 *dir32 = nullptr;
@@ -66,13 +67,16 @@ static int dev_alloc(f110_sim *s, T **p, size_t n, bool zero = true)
 #define TRY(x) do { int r_ = (x); if (r_) return r_; } while (0)
 
 // per-angle ray direction in the map frame and its reciprocals (1/0 stored as -inf, see trace32)
-static void build_dir_table(const double *sines, const double *cosines, int T, double oc, double os, std::vector<float4> &dir)
+static void build_dir_table(const double *sines, const double *cosines, int T, double oc, double os, std::vector<float4> &dir,
+                            std::vector<float2> &dir2)
 {
     dir.resize(T);
+    dir2.resize(T);
     for (int i = 0; i < T; i++) {
         float dx = (float)(cosines[i] * oc + sines[i] * os), dy = (float)(-cosines[i] * os + sines[i] * oc);
         float ix = dx != 0.f ? 1.0f / dx : -INFINITY, iy = dy != 0.f ? 1.0f / dy : -INFINITY;
         dir[i] = make_float4(dx, dy, ix, iy);
+        dir2[i] = make_float2(dx, dy);
     }
 }
 
@@ -122,6 +126,8 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
     // laser_models.py:367-368
     double angle_increment = cfg->fov / (cfg->n_beams - 1);
     d.theta_inc = cfg->theta_dis * angle_increment / (2. * M_PI);
+    d.inc_fix = (unsigned long long)(d.theta_inc * 4294967296.0 + 0.5);
+    d.kstep_lo = (unsigned)(32ull * d.inc_fix); d.kstep_hi = (unsigned)((32ull * d.inc_fix) >> 32);
     int rc = 0;
     do {
         // obs block: 7 state fields + collisions + lap_times + lap_counts, contiguous for a single D2H copy
@@ -164,6 +170,8 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
         d.beam_cos32 = tabs32; d.side_dist32 = tabs32 + B; d.ttc_k32 = tabs32 + 2 * B;
         if ((rc = dev_alloc(s, &s->dir32, (size_t)cfg->theta_dis))) break;
         d.dir32 = s->dir32;
+        if ((rc = dev_alloc(s, &s->dir2, (size_t)cfg->theta_dis))) break;
+        d.dir2 = s->dir2;
         double *params = nullptr;
         if ((rc = dev_alloc(s, &params, (A + 1) * F110_NP))) break;
         d.params = params;
@@ -195,6 +203,7 @@ extern "C" int f110_destroy(f110_sim *s)
     for (void *p : s->allocs) cudaFree(p);
     if (s->edt64) cudaFree(s->edt64);
     if (s->edt32) cudaFree(s->edt32);
+    if (s->edt32p) cudaFree(s->edt32p);
     if (s->edt_tex) cudaDestroyTextureObject(s->edt_tex);
     if (s->edt_arr) cudaFreeArray(s->edt_arr);
     if (s->noise) cudaFree(s->noise);
@@ -215,6 +224,7 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
     CK(cudaSetDevice(s->device));
     CK(cudaStreamSynchronize(st));
     if (s->edt64) { cudaFree(s->edt64); cudaFree(s->edt32); s->edt64 = nullptr; s->edt32 = nullptr; }
+    if (s->edt32p) { cudaFree(s->edt32p); s->edt32p = nullptr; }
     if (s->edt_tex) { cudaDestroyTextureObject(s->edt_tex); s->edt_tex = 0; }
     if (s->edt_arr) { cudaFreeArray(s->edt_arr); s->edt_arr = nullptr; }
     F110Dev &d = s->d;
@@ -234,6 +244,16 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
     d.edt64 = s->edt64; d.edt32 = s->edt32;
     f110_launch_edt32(s->edt64, s->edt32, cells, d.inv_res, s->cfg.eps, st);
     s->launches += 1;
+    if (d.scan_is_f32) {   // padded copy for the fp32 ray-cast (see scan32p)
+        d.pad = (int)ceil(s->cfg.max_range / res) + 2;
+        d.wp = w + 2 * d.pad;
+        size_t pcells = (size_t)d.wp * (h + 2 * d.pad);
+        if (pcells >= (1ull << 31)) return fail(F110_ERR_INVALID, "map too large for the padded fp32 layout");
+        CK(cudaMalloc(&s->edt32p, pcells * 4));
+        f110_launch_pad_edt32(s->edt32, s->edt32p, h, w, d.pad, d.oob32, st);
+        d.edt32p = s->edt32p;
+        s->launches += 1;
+    }
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(st));
     // the same fp32 map as a CUDA array behind a point-sampled texture (2D-local layout, floor + address in the TEX unit)
@@ -256,8 +276,10 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
         CK(cudaMemcpy(sn.data(), d.sines, d.theta_dis * 8, cudaMemcpyDeviceToHost));
         CK(cudaMemcpy(cs.data(), d.cosines, d.theta_dis * 8, cudaMemcpyDeviceToHost));
         std::vector<float4> dir;
-        build_dir_table(sn.data(), cs.data(), d.theta_dis, oc, os, dir);
+        std::vector<float2> dir2;
+        build_dir_table(sn.data(), cs.data(), d.theta_dis, oc, os, dir, dir2);
         CK(cudaMemcpy(s->dir32, dir.data(), dir.size() * sizeof(float4), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(s->dir2, dir2.data(), dir2.size() * sizeof(float2), cudaMemcpyHostToDevice));
     }
     return F110_OK;
 }
@@ -287,8 +309,10 @@ extern "C" int f110_set_tables(f110_sim *s, const double *sines, const double *c
     CK(cudaMemcpy((void *)d.beam_cos32, f.data(), f.size() * 4, cudaMemcpyHostToDevice));
     double oc = s->has_map ? d.oc : 1.0, os = s->has_map ? d.os : 0.0;
     std::vector<float4> dir;
-    build_dir_table(sines, cosines, T, oc, os, dir);
+    std::vector<float2> dir2;
+    build_dir_table(sines, cosines, T, oc, os, dir, dir2);
     CK(cudaMemcpy(s->dir32, dir.data(), dir.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(s->dir2, dir2.data(), dir2.size() * sizeof(float2), cudaMemcpyHostToDevice));
     s->has_tables = true;
     return F110_OK;
 }

@@ -13,6 +13,8 @@ struct F110Dev {
     int noise_mode, auto_reset, count_lookups, n_pool, scan_is_f32, env_offset;
     double timestep, fov, eps, max_range, theta_inc, ttc_thresh, noise_std;
     unsigned long long seed;
+    unsigned long long inc_fix;        // theta_inc in 32.32 fixed point; kstep = 32 * inc_fix (one round of 32 beams)
+    unsigned kstep_lo, kstep_hi;
     float max_c32, res32, noise_std32, ttc_thresh32, side_max32;   // fp32 path constants (cells / metres)
     // map
     int map_h, map_w, res_pow2, has_rot;
@@ -22,10 +24,13 @@ struct F110Dev {
     const double *edt64;               // row-major [h][w], metres
     const float *edt32;                // row-major [h][w], in CELL units (metres / res); obstacle cells hold 1024 (see fp32 kernels)
     unsigned long long edt_tex;        // cudaTextureObject_t over a CUDA array with the same content (point sampling)
+    const float *edt32p;               // edt32 with a border of `pad` cells on every side holding oob32: [h + 2 pad][wp]
+    int pad, wp;                       // pad >= max_range / res + 2, wp = w + 2 pad: a ray that starts inside the map never leaves it
     // tables
     const double *sines, *cosines;                  // theta_dis
     const double *scan_angles, *beam_cos, *side_dist;  // n_beams
     const float4 *dir32;                            // theta_dis: (dx, dy, 1/dx, 1/dy), unit ray direction in the map frame
+    const float2 *dir2;                             // theta_dis: (dx, dy) only (padded-map kernel)
     const float *beam_cos32, *side_dist32, *ttc_k32; // n_beams; ttc_k = 1.2 * ttc_thresh * |cos|
     const double *params;                           // (n_agents + 1) * F110_NP
     // per (env, agent)
@@ -65,3 +70,4 @@ void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, doubl
 void f110_launch_scan_only32(const F110Dev &d, const double *poses, int n, float *out, int variant, cudaStream_t st);
 void f110_launch_reset(const F110Dev &d, const double *poses_dev, const double *rot_dev, const uint8_t *mask_dev, cudaStream_t st);
 void f110_launch_edt32(const double *src, float *dst, size_t cells, double inv_res, double eps, cudaStream_t st);
+void f110_launch_pad_edt32(const float *src, float *dst, int h, int w, int pad, float oob, cudaStream_t st);
