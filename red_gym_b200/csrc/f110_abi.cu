@@ -252,6 +252,15 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
         CK(cudaMalloc(&s->edt32p, pcells * 4));
         f110_launch_pad_edt32(s->edt32, s->edt32p, h, w, d.pad, d.oob32, st);
         d.edt32p = s->edt32p;
+        // index bias of the mantissa-floor trick: bits(2^23 + n) = 0x4B000000 + n
+        for (unsigned cx = 0; ; cx += (1u << 21)) {
+            uint64_t k = ((uint64_t)0x4B000000u * (uint64_t)d.wp + 0x4B000000u + cx) & 0xffffffffull;
+            if (k + pcells < (1ull << 32)) {
+                d.magic_x = 8388608.0f + (float)cx;
+                d.edt32p_adj = (unsigned long long)s->edt32p - 4ull * k;
+                break;
+            }
+        }
         s->launches += 1;
     }
     CK(cudaGetLastError());

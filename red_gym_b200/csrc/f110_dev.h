@@ -25,6 +25,8 @@ struct F110Dev {
     const float *edt32;                // row-major [h][w], in CELL units (metres / res); obstacle cells hold 1024 (see fp32 kernels)
     unsigned long long edt_tex;        // cudaTextureObject_t over a CUDA array with the same content (point sampling)
     const float *edt32p;               // edt32 with a border of `pad` cells on every side holding oob32: [h + 2 pad][wp]
+    unsigned long long edt32p_adj;     // byte address of edt32p minus 4 * K, K = what the float exponent bits contribute (scan32p)
+    float magic_x;                     // 2^23 (+ 2^21 when K would wrap the 32-bit index)
     int pad, wp;                       // pad >= max_range / res + 2, wp = w + 2 pad: a ray that starts inside the map never leaves it
     // tables
     const double *sines, *cosines;                  // theta_dis
