@@ -17,6 +17,7 @@ COMMON = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "--expt-relax
 UNITS = [
     ("f110_kernels_fp64.cu", ["-fmad=false"]),
     ("f110_kernels_fp32.cu", []),
+    ("f110_order.cu", []),
     ("f110_abi.cu", []),
 ]
 

@@ -35,6 +35,9 @@ struct f110_sim {
     bool has_map = false, has_tables = false;
     double *edt64 = nullptr;
     float *edt32 = nullptr, *edt32p = nullptr;
+    int *order_hist = nullptr, *order_base = nullptr;
+    int *order_buf = nullptr;      // order | key | rank, NA each
+    bool use_order = false;
     float2 *dir2 = nullptr;
     cudaArray_t edt_arr = nullptr;
     cudaTextureObject_t edt_tex = 0;
@@ -186,6 +189,12 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
         cudaMemset(d.near_start, 1, NA);
     }
     d.actions = s->actions;
+    // spatial launch order: pays once more scans are in flight than the GPU holds at a time (and costs 3 small launches)
+    s->use_order = NA >= 32768 && !(cfg->raycast_variant & 64);
+    if (s->use_order) {
+        if (dev_alloc(s, &s->order_buf, 3 * NA)) { f110_destroy(s); return F110_ERR_NOMEM; }
+        d.order_chunk_envs = (A == 1 && N >= 8192) ? (int)((N + 7) / 8) : (int)N;   // same chunks as f110_step_host
+    }
     cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking);
     cudaEventCreate(&s->ev_a);
     cudaEventCreate(&s->ev_b);
@@ -204,6 +213,8 @@ extern "C" int f110_destroy(f110_sim *s)
     if (s->edt64) cudaFree(s->edt64);
     if (s->edt32) cudaFree(s->edt32);
     if (s->edt32p) cudaFree(s->edt32p);
+    if (s->order_hist) cudaFree(s->order_hist);
+    if (s->order_base) cudaFree(s->order_base);
     if (s->edt_tex) cudaDestroyTextureObject(s->edt_tex);
     if (s->edt_arr) cudaFreeArray(s->edt_arr);
     if (s->noise) cudaFree(s->noise);
@@ -262,6 +273,22 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
             }
         }
         s->launches += 1;
+    }
+    if (s->use_order) {
+        // tiles of >= 32 cells, at most 64 x 64 of them; 8 heading octants; chunk-major
+        int tile = 32;
+        while ((w + tile - 1) / tile > 64 || (h + tile - 1) / tile > 64) tile *= 2;
+        d.order_tx = (w + tile - 1) / tile; d.order_ty = (h + tile - 1) / tile;
+        d.order_inv_tile = 1.0f / (float)tile;
+        int chunks = (d.n_envs + d.order_chunk_envs - 1) / d.order_chunk_envs;
+        d.order_bins = chunks * d.order_tx * d.order_ty * 8;
+        if (s->order_hist) { cudaFree(s->order_hist); cudaFree(s->order_base); s->order_hist = s->order_base = nullptr; }
+        CK(cudaMalloc(&s->order_hist, (size_t)d.order_bins * 4));
+        CK(cudaMalloc(&s->order_base, (size_t)d.order_bins * 4));
+        CK(cudaMemsetAsync(s->order_hist, 0, (size_t)d.order_bins * 4, st));
+        const size_t NA = (size_t)d.n_envs * d.n_agents;
+        d.order = s->order_buf; d.order_key = s->order_buf + NA; d.order_rank = s->order_buf + 2 * NA;
+        d.order_hist = s->order_hist; d.order_base = s->order_base;
     }
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(st));
@@ -403,6 +430,7 @@ static int enqueue_step(f110_sim *s, const uint8_t *mask_dev, cudaStream_t st)
     F110Dev &d = s->d;
     d.step_mask = mask_dev;
     f110_launch_dynamics(d, st);
+    if (d.order) { f110_launch_order(d, st); s->launches += 3; }
     if (s->timing) cudaEventRecord(s->ev_a, st);
     if (d.scan_is_f32) f110_launch_raycast32(d, 0, d.n_envs, s->cfg.raycast_variant, st);
     else f110_launch_raycast64(d, 0, d.n_envs, s->cfg.raycast_variant, st);
@@ -466,6 +494,7 @@ extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *o
     d.step_mask = nullptr;
     f110_launch_dynamics(d, st);
     s->launches++;
+    if (d.order) { f110_launch_order(d, st); s->launches += 3; }
     // The scans dominate the D2H traffic.  With one agent per env nothing after the ray-cast touches
     // them, so the ray-cast is issued in env chunks and each chunk's copy-out (on a second stream)
     // overlaps the next chunk's kernel.
@@ -476,7 +505,7 @@ extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *o
         s->chunk_ev.resize(chunks);
         for (size_t i = old; i < s->chunk_ev.size(); i++) cudaEventCreateWithFlags(&s->chunk_ev[i], cudaEventDisableTiming);
     }
-    size_t per = (N + chunks - 1) / chunks;
+    size_t per = (N + chunks - 1) / chunks;     // == d.order_chunk_envs when the scans are ordered
     for (int c = 0; c < chunks; c++) {
         size_t b = c * per, cnt = (b + per <= N) ? per : (N > b ? N - b : 0);
         if (!cnt) break;

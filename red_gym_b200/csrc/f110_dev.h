@@ -60,6 +60,10 @@ struct F110Dev {
     const double *pool;      // [n_pool][A][3]
     unsigned long long *lookups;
     const uint8_t *step_mask;   // [N] or null: envs that take part in this step (masked reset)
+    // spatial launch order of the scans (f110_order.cu); order == null: warp w works on agent w
+    int *order, *order_key, *order_rank, *order_hist, *order_base;
+    int order_bins, order_tx, order_ty, order_chunk_envs;
+    float order_inv_tile;
 };
 
 // launch helpers implemented in the kernel translation units
@@ -72,4 +76,5 @@ void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, doubl
 void f110_launch_scan_only32(const F110Dev &d, const double *poses, int n, float *out, int variant, cudaStream_t st);
 void f110_launch_reset(const F110Dev &d, const double *poses_dev, const double *rot_dev, const uint8_t *mask_dev, cudaStream_t st);
 void f110_launch_edt32(const double *src, float *dst, size_t cells, double inv_res, double eps, cudaStream_t st);
+void f110_launch_order(const F110Dev &d, cudaStream_t st);      // (chunk, tile, heading) counting sort -> d.order
 void f110_launch_pad_edt32(const float *src, float *dst, int h, int w, int pad, float oob, cudaStream_t st);

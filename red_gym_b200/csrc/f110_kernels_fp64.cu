@@ -375,6 +375,7 @@ __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int en
     int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (w >= env_count * d.n_agents) return;
     int ia = env_begin * d.n_agents + w;
+    if (d.order) ia = d.order[ia];      // spatial launch order (f110_order.cu)
     int e = ia / d.n_agents;
     if (d.step_mask && !d.step_mask[e]) return;
     const int lane = threadIdx.x & 31;

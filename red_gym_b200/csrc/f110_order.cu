@@ -1,0 +1,96 @@
+// Spatial launch order of the lidar scans (sm_100a).
+//
+// The ray-cast is a chain of dependent 4/8-byte gathers from the EDT; what keeps it fast is that the cells a warp
+// walks are already in its SM's L1.  Warps that run on one SM at the same time therefore should belong to cars
+// that are close together and look the same way: they walk the same part of the map at the same time.  Right after
+// a reset env order is track order and that holds by construction; after some hundred steps of random actions and
+// auto-resets it does not, and the same kernel runs 1.3x slower (measured).  So before each ray-cast the
+// agents are put in (chunk, map tile, heading octant) order by a counting sort over small integer keys:
+//     k_order_count   key per agent, rank = atomicAdd(hist[key], 1)
+//     k_order_scan    exclusive prefix over the bins (one CTA), clears hist for the next step
+//     k_order_scatter order[base[key] + rank] = agent
+// The ray-cast kernels then map warp w to agent order[w].  Only the schedule changes: every scan still writes
+// its own rows, so results are bit-identical to the unordered launch (tests/test_gpu_step.py).
+#include <cuda_runtime.h>
+#include "f110_dev.h"
+
+__global__ void __launch_bounds__(256) k_order_count(const F110Dev d)
+{
+    const int NA = d.n_envs * d.n_agents;
+    int ia = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ia >= NA) return;
+    double px = d.state[ia], py = d.state[(size_t)NA + ia], yaw = d.state[4 * (size_t)NA + ia];
+    double xt = px - d.ox, yt = py - d.oy;
+    float gx = (float)((xt * d.oc + yt * d.os) * d.inv_res);
+    float gy = (float)((-xt * d.os + yt * d.oc) * d.inv_res);
+    int tx = min(max(__float2int_rd(gx * d.order_inv_tile), 0), d.order_tx - 1);
+    int ty = min(max(__float2int_rd(gy * d.order_inv_tile), 0), d.order_ty - 1);
+    int hb = __float2int_rd((float)yaw * 1.2732395447351628f) & 7;        // 8 / (2 pi)
+    int chunk = (ia / d.n_agents) / d.order_chunk_envs;
+    int key = ((chunk * d.order_ty + ty) * d.order_tx + tx) * 8 + hb;
+    d.order_key[ia] = key;
+    // warp-aggregated: neighbours in env order are often neighbours on the track (same bin); one atomic per distinct key
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned peers = __match_any_sync(__activemask(), key);
+    const int leader = __ffs(peers) - 1;
+    int first = 0;
+    if ((int)lane == leader) first = atomicAdd(d.order_hist + key, __popc(peers));
+    first = __shfl_sync(peers, first, leader);
+    d.order_rank[ia] = first + __popc(peers & ((1u << lane) - 1u));
+}
+
+// one CTA per chunk: exclusive prefix sum of that chunk's n bins into base (starting at the chunk's first agent,
+// which is known because every chunk holds a fixed env range), hist cleared
+__global__ void __launch_bounds__(1024) k_order_scan(int *__restrict__ hist, int *__restrict__ base, int n, int agents_per_chunk)
+{
+    __shared__ int warp_sum[32];
+    hist += (size_t)blockIdx.x * n;
+    base += (size_t)blockIdx.x * n;
+    const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
+    const int per = (n + 1023) / 1024;
+    const int lo = min(t * per, n), hi = min(lo + per, n);
+    int s = 0;
+    for (int i = lo; i < hi; i++) s += hist[i];
+    int inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    if (lane == 31) warp_sum[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        int w = warp_sum[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += v;
+        }
+        warp_sum[lane] = wi - w;
+    }
+    __syncthreads();
+    int run = blockIdx.x * agents_per_chunk + warp_sum[wid] + inc - s;
+    for (int i = lo; i < hi; i++) {
+        int h = hist[i];
+        base[i] = run;
+        hist[i] = 0;
+        run += h;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_order_scatter(const F110Dev d)
+{
+    const int NA = d.n_envs * d.n_agents;
+    int ia = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ia >= NA) return;
+    d.order[d.order_base[d.order_key[ia]] + d.order_rank[ia]] = ia;
+}
+
+void f110_launch_order(const F110Dev &d, cudaStream_t st)
+{
+    const int NA = d.n_envs * d.n_agents;
+    k_order_count<<<(NA + 255) / 256, 256, 0, st>>>(d);
+    const int chunks = (d.n_envs + d.order_chunk_envs - 1) / d.order_chunk_envs;
+    k_order_scan<<<chunks, 1024, 0, st>>>(d.order_hist, d.order_base, d.order_bins / chunks, d.order_chunk_envs * d.n_agents);
+    k_order_scatter<<<(NA + 255) / 256, 256, 0, st>>>(d);
+}
