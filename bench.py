@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- agent-steps/s of the batched F1TENTH step (1080-beam lidar) on N B200s.
 
-    python bench.py [--gpus N --steps K --warmup W] [--workload config3|config2|config4] [--impl reference]
+    python bench.py [--gpus N --steps K --warmup W] [--workload config3|config2|config4|config5] [--impl reference]
 
 One "step" = one pass of the hot path (dynamics -> lidar -> iTTC -> [GJK, opponent ray-cast] -> laps) over
 every env of the batch.  Workloads follow BASELINE.json `configs`:
@@ -283,6 +283,75 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def run_sweep(args):
+    """BASELINE config 5: ray-cast only, B in {270, 1080, 2160} x EDT size {1024, 2048, 4096}^2 (example_map resampled),
+    2^18 poses per GPU uniform over free space (clearance 0.3 m), through f110_raycast.  One JSON line, `sweep` = list
+    of points (scans/s, rays/s, EDT lookups/s, algorithmic GB/s); L2 hit rate and DRAM bytes per point come from the
+    ncu captures under profiles/."""
+    import torch
+    import torch.distributed as dist
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200 import host
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    n = args.envs or (1 << 18)
+    sizes = [int(x) for x in args.sweep_sizes.split(",")]
+    beams = [int(x) for x in args.sweep_beams.split(",")]
+    dtypes = [args.dtype] if args.dtype else ["fp32", "fp64"]
+    K, W = max(args.steps, 1), max(args.warmup, 3)
+    points = []
+    for size in sizes:
+        m = host.resampled_map(size)
+        poses = torch.from_numpy(host.free_space_poses(m, n, seed=7 + rank)).to(device)
+        for dtype in dtypes:
+            esz = 4 if dtype == "fp32" else 8
+            for B in beams:
+                env = BatchF110Env(num_envs=1, num_agents=1, device=local, dtype=dtype, noise="off", num_beams=B, map_data=m,
+                                   raycast_variant=args.variant)
+                out = torch.empty((n, B), dtype=torch.float32 if dtype == "fp32" else torch.float64, device=device)
+                for _ in range(W):
+                    env.raycast(poses, out)
+                if world > 1:
+                    dist.barrier()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(K):
+                    env.raycast(poses, out)
+                e1.record()
+                torch.cuda.synchronize()
+                t = torch.tensor([e0.elapsed_time(e1) / K], device=device, dtype=torch.float64)
+                if world > 1:
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t.item())
+                env.count_lookups(True)
+                env.raycast(poses, out)
+                torch.cuda.synchronize()
+                lk = env.lookups() / float(n) + (B - 1)          # reference definition: one lookup per distance_transform call
+                env.count_lookups(False)
+                scans_s = n * world / (ms * 1e-3)
+                points.append({"edt": size, "beams": B, "dtype": "f32" if dtype == "fp32" else "f64", "ms_per_launch": ms,
+                               "scans_per_s": scans_s, "rays_per_s": scans_s * B, "lookups_per_scan": lk,
+                               "lookups_per_s": scans_s * lk, "algorithmic_GBps": scans_s * (lk + B) * esz / 1e9,
+                               "edt_MB": size * size * esz / 1e6})
+                env.close()
+                del out
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        print(json.dumps({"metric": "scans/s (ray-cast only sweep, config 5)", "unit": "scans/s", "n_gpus": world, "steps": K, "warmup": W,
+                          "value": max(p["scans_per_s"] for p in points), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                          "data": "synthetic", "config": {"workload": "config5", "poses_per_gpu": n, "map": "example_map resampled",
+                                                          "pose_sampling": "uniform over free cells with clearance 0.3 m, seed 7 + rank"},
+                          "hbm_peak_GBps": peak, "peak_source": peak_src, "sweep": points}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def cpu_reference(workload, seconds=12.0, nthreads=0):
     """The CPU restatement of the reference (oracle/, pthreads over envs) on a bounded sample of the workload."""
     sys.path.insert(0, os.path.join(REPO, "oracle"))
@@ -335,7 +404,9 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS) + ["config5"])
+    ap.add_argument("--sweep-sizes", default="1024,2048,4096")
+    ap.add_argument("--sweep-beams", default="270,1080,2160")
     ap.add_argument("--envs", type=int, default=0, help="override envs per GPU")
     ap.add_argument("--dtype", default=None, choices=["fp32", "fp64"])
     ap.add_argument("--variant", type=int, default=0, help="raycast kernel variant (bit2: fp32 lookups through the texture unit)")
@@ -345,7 +416,12 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
-    if args.impl == "reference":
+    if args.workload == "config5":
+        if args.impl == "reference":
+            print(json.dumps({"impl": "reference", "unavailable": "the sweep is a GPU-only diagnostic; use --workload config3"}))
+        else:
+            run_sweep(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_b200(args)

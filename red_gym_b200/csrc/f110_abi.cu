@@ -37,6 +37,8 @@ struct f110_sim {
     float *edt32 = nullptr, *edt32p = nullptr;
     int *order_hist = nullptr, *order_base = nullptr;
     int *order_buf = nullptr;      // order | key | rank, NA each
+    int *rc_order_buf = nullptr;   // the same for f110_raycast, grown on demand
+    size_t rc_order_cap = 0;
     bool use_order = false;
     float2 *dir2 = nullptr;
     cudaArray_t edt_arr = nullptr;
@@ -215,6 +217,7 @@ extern "C" int f110_destroy(f110_sim *s)
     if (s->edt32p) cudaFree(s->edt32p);
     if (s->order_hist) cudaFree(s->order_hist);
     if (s->order_base) cudaFree(s->order_base);
+    if (s->rc_order_buf) cudaFree(s->rc_order_buf);
     if (s->edt_tex) cudaDestroyTextureObject(s->edt_tex);
     if (s->edt_arr) cudaFreeArray(s->edt_arr);
     if (s->noise) cudaFree(s->noise);
@@ -251,9 +254,13 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
     d.has_rot = !(oc == 1.0 && os == 0.0);
     d.max_c32 = (float)(s->cfg.max_range / res); d.res32 = (float)res;
     d.oob64 = edt[cells - 1];             // dt[-1, -1]
-    d.oob32 = edt[cells - 1] > s->cfg.eps ? (float)(edt[cells - 1] / res) : 1024.0f;
+    // fp32 encoding: free cells min(dist, cap), obstacle cells `sent`, max_range < cap < sent (all in cells)
+    const float cap = floorf(d.max_c32) + 2.0f;
+    d.sent32 = 1024.0f;
+    while (d.sent32 <= cap) d.sent32 *= 2.0f;
+    d.oob32 = edt[cells - 1] > s->cfg.eps ? fminf((float)(edt[cells - 1] / res), cap) : d.sent32;
     d.edt64 = s->edt64; d.edt32 = s->edt32;
-    f110_launch_edt32(s->edt64, s->edt32, cells, d.inv_res, s->cfg.eps, st);
+    f110_launch_edt32(s->edt64, s->edt32, cells, d.inv_res, s->cfg.eps, cap, d.sent32, st);
     s->launches += 1;
     if (d.scan_is_f32) {   // padded copy for the fp32 ray-cast (see scan32p)
         d.pad = (int)ceil(s->cfg.max_range / res) + 2;
@@ -274,8 +281,9 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
         }
         s->launches += 1;
     }
-    if (s->use_order) {
-        // tiles of >= 32 cells, at most 64 x 64 of them; 8 heading octants; chunk-major
+    {
+        // spatial launch order: tiles of >= 32 cells, at most 64 x 64 of them; 8 heading octants; chunk-major
+        if (!d.order_chunk_envs) d.order_chunk_envs = d.n_envs;
         int tile = 32;
         while ((w + tile - 1) / tile > 64 || (h + tile - 1) / tile > 64) tile *= 2;
         d.order_tx = (w + tile - 1) / tile; d.order_ty = (h + tile - 1) / tile;
@@ -287,7 +295,7 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
         CK(cudaMalloc(&s->order_base, (size_t)d.order_bins * 4));
         CK(cudaMemsetAsync(s->order_hist, 0, (size_t)d.order_bins * 4, st));
         const size_t NA = (size_t)d.n_envs * d.n_agents;
-        d.order = s->order_buf; d.order_key = s->order_buf + NA; d.order_rank = s->order_buf + 2 * NA;
+        if (s->use_order) { d.order = s->order_buf; d.order_key = s->order_buf + NA; d.order_rank = s->order_buf + 2 * NA; }
         d.order_hist = s->order_hist; d.order_base = s->order_base;
     }
     CK(cudaGetLastError());
@@ -540,8 +548,21 @@ extern "C" int f110_raycast(f110_sim *s, const double *poses_dev, int32_t n, voi
     if (n == 0) return F110_OK;
     if (!poses_dev || !out_dev || n < 0) return fail(F110_ERR_INVALID, "bad raycast arguments");
     CK(cudaSetDevice(s->device));
-    if (s->d.scan_is_f32) f110_launch_scan_only32(s->d, poses_dev, n, (float *)out_dev, s->cfg.raycast_variant, (cudaStream_t)stream);
-    else f110_launch_scan_only64(s->d, poses_dev, n, (double *)out_dev, s->cfg.raycast_variant, (cudaStream_t)stream);
+    const int *order = nullptr;
+    if (n >= 32768 && !(s->cfg.raycast_variant & 64)) {    // same reasoning as in the step: neighbours in launch order = neighbours on the map
+        if ((size_t)n > s->rc_order_cap) {
+            CK(cudaStreamSynchronize((cudaStream_t)stream));
+            if (s->rc_order_buf) cudaFree(s->rc_order_buf);
+            s->rc_order_buf = nullptr; s->rc_order_cap = 0;
+            CK(cudaMalloc(&s->rc_order_buf, 3 * (size_t)n * 4));
+            s->rc_order_cap = n;
+        }
+        f110_launch_order_poses(s->d, poses_dev, n, s->rc_order_buf, (cudaStream_t)stream);
+        s->launches += 3;
+        order = s->rc_order_buf;
+    }
+    if (s->d.scan_is_f32) f110_launch_scan_only32(s->d, poses_dev, n, (float *)out_dev, order, s->cfg.raycast_variant, (cudaStream_t)stream);
+    else f110_launch_scan_only64(s->d, poses_dev, n, (double *)out_dev, order, s->cfg.raycast_variant, (cudaStream_t)stream);
     s->launches++;
     CK(cudaGetLastError());
     return F110_OK;

@@ -15,14 +15,14 @@ struct F110Dev {
     unsigned long long seed;
     unsigned long long inc_fix;        // theta_inc in 32.32 fixed point; kstep = 32 * inc_fix (one round of 32 beams)
     unsigned kstep_lo, kstep_hi;
-    float max_c32, res32, noise_std32, ttc_thresh32, side_max32;   // fp32 path constants (cells / metres)
+    float max_c32, res32, noise_std32, ttc_thresh32, side_max32, sent32;   // fp32 path constants (cells / metres)
     // map
     int map_h, map_w, res_pow2, has_rot;
     double res, inv_res, ox, oy, oc, os, xmax, ymax;
     double oob64;                      // dt[-1,-1] : value an out-of-map lookup returns
     float oob32;
     const double *edt64;               // row-major [h][w], metres
-    const float *edt32;                // row-major [h][w], in CELL units (metres / res); obstacle cells hold 1024 (see fp32 kernels)
+    const float *edt32;                // row-major [h][w], in CELL units (metres / res); obstacle cells hold sent32 (see fp32 kernels)
     unsigned long long edt_tex;        // cudaTextureObject_t over a CUDA array with the same content (point sampling)
     const float *edt32p;               // edt32 with a border of `pad` cells on every side holding oob32: [h + 2 pad][wp]
     unsigned long long edt32p_adj;     // byte address of edt32p minus 4 * K, K = what the float exponent bits contribute (scan32p)
@@ -72,9 +72,11 @@ void f110_launch_raycast64(const F110Dev &d, int env_begin, int env_count, int v
 void f110_launch_raycast32(const F110Dev &d, int env_begin, int env_count, int variant, cudaStream_t st);
 void f110_launch_agents(const F110Dev &d, cudaStream_t st);      // GJK + opponent ray-cast (A >= 2)
 void f110_launch_finalize(const F110Dev &d, cudaStream_t st);    // collisions, lap bookkeeping, done
-void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, double *out, int variant, cudaStream_t st);
-void f110_launch_scan_only32(const F110Dev &d, const double *poses, int n, float *out, int variant, cudaStream_t st);
+// order: null or a permutation of [0, n): warp w scans pose order[w]
+void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, double *out, const int *order, int variant, cudaStream_t st);
+void f110_launch_scan_only32(const F110Dev &d, const double *poses, int n, float *out, const int *order, int variant, cudaStream_t st);
 void f110_launch_reset(const F110Dev &d, const double *poses_dev, const double *rot_dev, const uint8_t *mask_dev, cudaStream_t st);
-void f110_launch_edt32(const double *src, float *dst, size_t cells, double inv_res, double eps, cudaStream_t st);
+void f110_launch_edt32(const double *src, float *dst, size_t cells, double inv_res, double eps, float cap, float sent, cudaStream_t st);
 void f110_launch_order(const F110Dev &d, cudaStream_t st);      // (chunk, tile, heading) counting sort -> d.order
+void f110_launch_order_poses(const F110Dev &d, const double *poses, int n, int *buf, cudaStream_t st);
 void f110_launch_pad_edt32(const float *src, float *dst, int h, int w, int pad, float oob, cudaStream_t st);

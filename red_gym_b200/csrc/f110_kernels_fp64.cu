@@ -408,10 +408,11 @@ __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int en
 
 template <bool ROT, bool POW2, bool COUNT>
 __global__ void __launch_bounds__(256) k_scan_only64(const F110Dev d, const double *__restrict__ poses, int n,
-                                                     double *__restrict__ out)
+                                                     double *__restrict__ out, const int *__restrict__ order)
 {
     int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (w >= n) return;
+    if (order) w = order[w];
     bool hit = false;
     unsigned nlook = 0;
     scan_rounds<ROT, POW2, false, COUNT>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], out + (size_t)w * d.n_beams,
@@ -456,11 +457,11 @@ void f110_launch_raycast64(const F110Dev &d, int env_begin, int env_count, int v
 #undef RC64
 }
 
-void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, double *out, int variant, cudaStream_t st)
+void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, double *out, const int *order, int variant, cudaStream_t st)
 {
     int grid = (int)(((long long)n * 32 + 255) / 256);
     if (grid == 0) return;
-    DISPATCH64(k_scan_only64, grid, d, poses, n, out);
+    DISPATCH64(k_scan_only64, grid, d, poses, n, out, order);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -786,15 +787,18 @@ void f110_launch_reset(const F110Dev &d, const double *poses_dev, const double *
 // ------------------------------------------------------------------------------------------------
 // fp32 copy of the EDT in CELL units (metres / resolution) for the fast path
 // ------------------------------------------------------------------------------------------------
-__global__ void k_edt32(const double *__restrict__ src, float *__restrict__ dst, size_t cells, double inv_res, double eps)
+// free cells: min(distance in cells, cap) with cap > max_range in cells (a larger value ends the ray at max range all the same);
+// obstacle cells (dist <= eps, where trace_ray stops): the sentinel `sent` > cap (see the fp32 kernels)
+__global__ void k_edt32(const double *__restrict__ src, float *__restrict__ dst, size_t cells, double inv_res, double eps,
+                        float cap, float sent)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < cells) {
         double v = src[i];
-        dst[i] = (v > eps) ? (float)(v * inv_res) : 1024.0f;   // trace_ray stops when dist <= eps: sentinel (fp32 kernels)
+        dst[i] = (v > eps) ? fminf((float)(v * inv_res), cap) : sent;
     }
 }
-void f110_launch_edt32(const double *src, float *dst, size_t cells, double inv_res, double eps, cudaStream_t st)
+void f110_launch_edt32(const double *src, float *dst, size_t cells, double inv_res, double eps, float cap, float sent, cudaStream_t st)
 {
-    k_edt32<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(src, dst, cells, inv_res, eps);
+    k_edt32<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(src, dst, cells, inv_res, eps, cap, sent);
 }

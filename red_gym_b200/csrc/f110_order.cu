@@ -14,21 +14,24 @@
 #include <cuda_runtime.h>
 #include "f110_dev.h"
 
-__global__ void __launch_bounds__(256) k_order_count(const F110Dev d)
+// poses are read as x[i * stride], y[i * stride], yaw[i * stride]: the SoA state of a handle (stride 1) or an
+// (n, 3) pose array handed to f110_raycast (stride 3)
+__global__ void __launch_bounds__(256) k_order_count(const F110Dev d, const double *__restrict__ x, const double *__restrict__ y,
+                                                     const double *__restrict__ yawp, int stride, int n, int agents, int chunk_envs,
+                                                     int *__restrict__ keys, int *__restrict__ ranks)
 {
-    const int NA = d.n_envs * d.n_agents;
     int ia = blockIdx.x * blockDim.x + threadIdx.x;
-    if (ia >= NA) return;
-    double px = d.state[ia], py = d.state[(size_t)NA + ia], yaw = d.state[4 * (size_t)NA + ia];
+    if (ia >= n) return;
+    double px = x[(size_t)ia * stride], py = y[(size_t)ia * stride], yaw = yawp[(size_t)ia * stride];
     double xt = px - d.ox, yt = py - d.oy;
     float gx = (float)((xt * d.oc + yt * d.os) * d.inv_res);
     float gy = (float)((-xt * d.os + yt * d.oc) * d.inv_res);
     int tx = min(max(__float2int_rd(gx * d.order_inv_tile), 0), d.order_tx - 1);
     int ty = min(max(__float2int_rd(gy * d.order_inv_tile), 0), d.order_ty - 1);
     int hb = __float2int_rd((float)yaw * 1.2732395447351628f) & 7;        // 8 / (2 pi)
-    int chunk = (ia / d.n_agents) / d.order_chunk_envs;
+    int chunk = (ia / agents) / chunk_envs;
     int key = ((chunk * d.order_ty + ty) * d.order_tx + tx) * 8 + hb;
-    d.order_key[ia] = key;
+    keys[ia] = key;
     // warp-aggregated: neighbours in env order are often neighbours on the track (same bin); one atomic per distinct key
     const unsigned lane = threadIdx.x & 31;
     const unsigned peers = __match_any_sync(__activemask(), key);
@@ -36,7 +39,7 @@ __global__ void __launch_bounds__(256) k_order_count(const F110Dev d)
     int first = 0;
     if ((int)lane == leader) first = atomicAdd(d.order_hist + key, __popc(peers));
     first = __shfl_sync(peers, first, leader);
-    d.order_rank[ia] = first + __popc(peers & ((1u << lane) - 1u));
+    ranks[ia] = first + __popc(peers & ((1u << lane) - 1u));
 }
 
 // one CTA per chunk: exclusive prefix sum of that chunk's n bins into base (starting at the chunk's first agent,
@@ -78,19 +81,29 @@ __global__ void __launch_bounds__(1024) k_order_scan(int *__restrict__ hist, int
     }
 }
 
-__global__ void __launch_bounds__(256) k_order_scatter(const F110Dev d)
+__global__ void __launch_bounds__(256) k_order_scatter(const int *__restrict__ base, const int *__restrict__ keys,
+                                                       const int *__restrict__ ranks, int *__restrict__ order, int n)
 {
-    const int NA = d.n_envs * d.n_agents;
     int ia = blockIdx.x * blockDim.x + threadIdx.x;
-    if (ia >= NA) return;
-    d.order[d.order_base[d.order_key[ia]] + d.order_rank[ia]] = ia;
+    if (ia >= n) return;
+    order[base[keys[ia]] + ranks[ia]] = ia;
 }
 
 void f110_launch_order(const F110Dev &d, cudaStream_t st)
 {
     const int NA = d.n_envs * d.n_agents;
-    k_order_count<<<(NA + 255) / 256, 256, 0, st>>>(d);
+    k_order_count<<<(NA + 255) / 256, 256, 0, st>>>(d, d.state, d.state + NA, d.state + 4 * (size_t)NA, 1, NA, d.n_agents,
+                                                    d.order_chunk_envs, d.order_key, d.order_rank);
     const int chunks = (d.n_envs + d.order_chunk_envs - 1) / d.order_chunk_envs;
     k_order_scan<<<chunks, 1024, 0, st>>>(d.order_hist, d.order_base, d.order_bins / chunks, d.order_chunk_envs * d.n_agents);
-    k_order_scatter<<<(NA + 255) / 256, 256, 0, st>>>(d);
+    k_order_scatter<<<(NA + 255) / 256, 256, 0, st>>>(d.order_base, d.order_key, d.order_rank, d.order, NA);
+}
+
+// order of n stand-alone poses (f110_raycast): one chunk; buf = order | key | rank, n each
+void f110_launch_order_poses(const F110Dev &d, const double *poses, int n, int *buf, cudaStream_t st)
+{
+    int *order = buf, *keys = buf + n, *ranks = buf + 2 * (size_t)n;
+    k_order_count<<<(n + 255) / 256, 256, 0, st>>>(d, poses, poses + 1, poses + 2, 3, n, 1, n, keys, ranks);
+    k_order_scan<<<1, 1024, 0, st>>>(d.order_hist, d.order_base, d.order_tx * d.order_ty * 8, 0);
+    k_order_scatter<<<(n + 255) / 256, 256, 0, st>>>(d.order_base, keys, ranks, order, n);
 }

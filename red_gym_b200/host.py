@@ -130,3 +130,33 @@ def raceline_poses(n, csv_path=None, lateral=0.0, seed=0):
         poses[:, 0] += -off * np.sin(poses[:, 2])
         poses[:, 1] += off * np.cos(poses[:, 2])
     return poses
+
+
+def resampled_map(size, base_map=None, map_ext=".png"):
+    """BASELINE config 5: example_map resampled with PIL NEAREST to size x size cells covering the same
+    100 m x 100 m, re-thresholded like set_map, EDT by scipy.  Returns a MapData."""
+    import yaml
+    from PIL import Image
+    from scipy.ndimage import distance_transform_edt
+    base_map = base_map or os.path.join(MAPS_DIR, "example_map.yaml")
+    img = Image.open(os.path.splitext(base_map)[0] + map_ext).transpose(Image.FLIP_TOP_BOTTOM)
+    with open(base_map, "r") as stream:
+        meta = yaml.safe_load(stream)
+    extent = float(meta["resolution"]) * img.size[0]
+    occ = np.asarray(img.resize((size, size), Image.NEAREST), dtype=np.float64)
+    res = extent / size
+    edt = res * distance_transform_edt(occ > 128.0)
+    return MapData.from_arrays(edt, res, tuple(float(o) for o in meta["origin"]))
+
+
+def free_space_poses(m, n, seed=7, clearance=0.3):
+    """n poses uniform over the cells of MapData m that are more than `clearance` metres from an obstacle,
+    heading ~ U(0, 2 pi) (config 5)."""
+    rng = np.random.default_rng(seed)
+    free = np.argwhere(m.edt > clearance)
+    pick = free[rng.integers(0, free.shape[0], n)]
+    gx = (pick[:, 1] + rng.uniform(0, 1, n)) * m.resolution
+    gy = (pick[:, 0] + rng.uniform(0, 1, n)) * m.resolution
+    x = m.origin[0] + gx * m.orig_c - gy * m.orig_s
+    y = m.origin[1] + gx * m.orig_s + gy * m.orig_c
+    return np.stack([x, y, rng.uniform(0, 2 * np.pi, n)], axis=1)

@@ -129,3 +129,51 @@ def test_scan_before_map_raises_like_reference():
     b = sim.scan(d["poses"][0], r)
     c = sim.scan(d["poses"][0], r)
     assert (a == b).all() and not (b == c).all()
+
+
+@pytest.mark.parametrize("dtype", ["fp32", "fp64"])
+def test_raycast_spatial_order_is_only_a_schedule(dtype):
+    """f110_raycast launches >= 32768 poses in (tile, heading) order (f110_order.cu); the result must be bit-identical
+    to the plain launch (raycast_variant=64), on a resampled map (config 5) with poses all over free space."""
+    from red_gym_b200 import BatchF110Env, host
+    import torch
+    m = host.resampled_map(1024)
+    poses = host.free_space_poses(m, 40000, seed=7)
+    kw = dict(num_envs=1, num_agents=1, dtype=dtype, noise="off", num_beams=270, map_data=m)
+    a = BatchF110Env(**kw)
+    b = BatchF110Env(raycast_variant=64, **kw)
+    ra, rb = a.raycast(poses), b.raycast(poses)
+    assert a.launch_count == b.launch_count + 3
+    assert (ra == rb).all()
+    md = {"dt": m.edt, "h": m.height, "w": m.width, "res": m.resolution, "ox": m.origin[0], "oy": m.origin[1],
+          "oc": m.orig_c, "os": m.orig_s}
+    ora = fo.OracleEnv(1, 1, map_data=md, noise=False, num_beams=270)
+    want = ora.scan(poses[:2000])
+    got = ra[:2000].cpu().numpy()
+    if dtype == "fp64":
+        assert (got == want).all()
+    else:
+        d = np.abs(got - want)
+        assert np.median(d) < 1e-3 and (d > 2e-2).mean() < 0.03
+
+
+@pytest.mark.parametrize("size,res", [(700, 0.02), (2300, 0.05)])
+def test_fp32_sentinel_and_cap_scale_with_the_map(size, res):
+    """The fp32 EDT encodes obstacle cells as a sentinel above max_range (in cells) and caps free cells below it:
+    (700, 0.02) has max_range = 1500 cells (> the old fixed sentinel 1024); (2300, 0.05) has free cells more than
+    1024 cells away from any wall.  Both must agree with the fp64 oracle within the fp32 tolerance."""
+    from red_gym_b200 import BatchF110Env, host
+    from scipy.ndimage import distance_transform_edt
+    free = np.ones((size, size), dtype=bool)
+    free[:3, :] = free[-3:, :] = free[:, :3] = free[:, -3:] = False
+    free[size // 3:size // 3 + 20, size // 4:size // 2] = False
+    edt = res * distance_transform_edt(free)
+    m = host.MapData.from_arrays(edt, res, (-3.0, -2.0, 0.0))
+    poses = host.free_space_poses(m, 600, seed=3, clearance=0.2)
+    env = BatchF110Env(num_envs=1, num_agents=1, dtype="fp32", noise="off", map_data=m)
+    got = env.raycast(poses).cpu().numpy()
+    md = {"dt": m.edt, "h": m.height, "w": m.width, "res": m.resolution, "ox": m.origin[0], "oy": m.origin[1],
+          "oc": m.orig_c, "os": m.orig_s}
+    want = fo.OracleEnv(1, 1, map_data=md, noise=False).scan(poses)
+    d = np.abs(got - want)
+    assert np.median(d) < 1e-3 and (d > 2e-2).mean() < 0.03, (np.median(d), (d > 2e-2).mean(), d.max())
