@@ -166,6 +166,39 @@ int f110_last_raycast_ms(f110_sim *sim, float *ms);
 int64_t f110_launch_count(f110_sim *sim);
 int f110_synchronize(f110_sim *sim, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Scan -> bird's-eye bitmap.  Replaces weap_util.lidar.lidar_to_bitmap
+ * (weap_util/weap_util/lidar.py:114-154 and its OpenCV calls) for a batch of scans on the device;
+ * output bytes are identical to the reference's single-channel image.
+ * ------------------------------------------------------------------------------------------- */
+#define F110_BITMAP_FILL 0
+#define F110_BITMAP_POLYGON 1
+#define F110_BITMAP_RAYS 2
+
+typedef struct f110_bitmap_config {
+    int32_t abi_version;       /* F110_ABI_VERSION */
+    int32_t n_beams;           /* len(scan) */
+    int32_t target_beam_count; /* lidar.py:13 (600); 0 < target_beam_count < n_beams (:50) */
+    int32_t height, width;     /* output_image_dims (:12) */
+    int32_t draw_mode;         /* F110_BITMAP_* (:15) */
+    int32_t draw_center;       /* :11 */
+    int32_t bg_white;          /* bg_color == 'white' (:10): background 255, drawing 0; else 0 / 255 */
+    int32_t scan_is_f32;       /* scans are float (fp32 fast path) or double */
+    double scaling_factor;     /* resolved by the caller: min(dims) / max_scan_radius when that is given (:53-54) */
+} f110_bitmap_config;
+
+typedef struct f110_bitmap f110_bitmap;
+
+/* indices: host [target_beam_count] int32 = np.linspace(0, n_beams - 1, T, dtype=int) (:66);
+ * cos_a / sin_a: host [T] doubles = np.cos / np.sin(starting_angle + dir * fov * np.linspace(0, 1, T)) (:70,:75-76),
+ * computed by the host with numpy exactly as the reference does. */
+int f110_bitmap_create(const f110_bitmap_config *cfg, const int32_t *indices, const double *cos_a, const double *sin_a,
+                       int device, f110_bitmap **out);
+int f110_bitmap_destroy(f110_bitmap *bm);
+/* scans_dev: DEVICE [n][n_beams]; out_dev: DEVICE [n][height][width] bytes, or, with packed != 0,
+ * [n][height][ceil(width / 32)] 32-bit words, bit b of word k = pixel 32 k + b, set = drawn colour. */
+int f110_bitmap_render(f110_bitmap *bm, const void *scans_dev, int64_t n, void *out_dev, int32_t packed, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -22,7 +22,9 @@ NOISE_OFF, NOISE_TABLE, NOISE_PHILOX = 0, 1, 2
 EXPORTS = ["f110_last_error", "f110_abi_version", "f110_device_count", "f110_create", "f110_destroy",
            "f110_set_map", "f110_set_tables", "f110_set_params", "f110_set_noise_rows", "f110_set_reset_pool",
            "f110_reset", "f110_step", "f110_step_host", "f110_raycast", "f110_get_buffers", "f110_get_config",
-           "f110_count_lookups", "f110_enable_timing", "f110_last_raycast_ms", "f110_launch_count", "f110_synchronize"]
+           "f110_count_lookups", "f110_enable_timing", "f110_last_raycast_ms", "f110_launch_count", "f110_synchronize",
+           "f110_bitmap_create", "f110_bitmap_destroy", "f110_bitmap_render"]
+BITMAP_MODES = {"FILL": 0, "POLYGON": 1, "RAYS": 2}
 
 
 class Config(ctypes.Structure):
@@ -33,6 +35,13 @@ class Config(ctypes.Structure):
                 ("timestep", ctypes.c_double), ("fov", ctypes.c_double), ("eps", ctypes.c_double),
                 ("max_range", ctypes.c_double), ("ttc_thresh", ctypes.c_double), ("noise_std", ctypes.c_double),
                 ("seed", ctypes.c_uint64)]
+
+
+class BitmapConfig(ctypes.Structure):
+    _fields_ = [("abi_version", ctypes.c_int32), ("n_beams", ctypes.c_int32), ("target_beam_count", ctypes.c_int32),
+                ("height", ctypes.c_int32), ("width", ctypes.c_int32), ("draw_mode", ctypes.c_int32),
+                ("draw_center", ctypes.c_int32), ("bg_white", ctypes.c_int32), ("scan_is_f32", ctypes.c_int32),
+                ("scaling_factor", ctypes.c_double)]
 
 
 class Buffers(ctypes.Structure):
@@ -78,6 +87,9 @@ def load():
     L.f110_launch_count.argtypes = [vp]
     L.f110_launch_count.restype = i64
     L.f110_synchronize.argtypes = [vp, vp]
+    L.f110_bitmap_create.argtypes = [ctypes.POINTER(BitmapConfig), vp, vp, vp, ctypes.c_int, ctypes.POINTER(vp)]
+    L.f110_bitmap_destroy.argtypes = [vp]
+    L.f110_bitmap_render.argtypes = [vp, vp, i64, vp, i32, vp]
     for name in EXPORTS:
         fn = getattr(L, name)
         if name not in ("f110_last_error", "f110_launch_count"):

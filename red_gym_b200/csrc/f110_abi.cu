@@ -9,6 +9,7 @@
 #include <vector>
 #include "../../include/f110_b200.h"
 #include "f110_dev.h"
+#include "f110_bitmap_dev.h"
 
 static thread_local std::string g_err;
 static int fail(int code, const char *fmt, ...)
@@ -616,5 +617,82 @@ extern "C" int f110_synchronize(f110_sim *s, void *stream)
     if (!s) return fail(F110_ERR_INVALID, "null handle");
     CK(cudaSetDevice(s->device));
     CK(cudaStreamSynchronize((cudaStream_t)stream));
+    return F110_OK;
+}
+
+// ---- scan -> bitmap rasteriser (f110_bitmap.cu) -------------------------------------------------------------------
+struct f110_bitmap {
+    f110_bitmap_config cfg;
+    int device;
+    F110BitmapDev d;
+    void *tables = nullptr;
+    long long launches = 0;
+};
+
+extern "C" int f110_bitmap_create(const f110_bitmap_config *cfg, const int32_t *indices, const double *cos_a, const double *sin_a,
+                                  int device, f110_bitmap **out)
+{
+    if (!cfg || !indices || !cos_a || !sin_a || !out) return fail(F110_ERR_INVALID, "null argument");
+    if (cfg->abi_version != F110_ABI_VERSION) return fail(F110_ERR_INVALID, "abi_version %d != %d", cfg->abi_version, F110_ABI_VERSION);
+    if (cfg->height < 1 || cfg->width < 1) return fail(F110_ERR_INVALID, "output_image_dims must be at least 1x1");
+    if (!(cfg->target_beam_count > 0 && cfg->target_beam_count < cfg->n_beams))
+        return fail(F110_ERR_INVALID, "need 0 < target_beam_count < len(scan)");
+    if (cfg->draw_mode < F110_BITMAP_FILL || cfg->draw_mode > F110_BITMAP_RAYS) return fail(F110_ERR_INVALID, "bad draw_mode");
+    for (int i = 0; i < cfg->target_beam_count; i++)
+        if (indices[i] < 0 || indices[i] >= cfg->n_beams) return fail(F110_ERR_INVALID, "beam index out of range");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(F110_ERR_CUDA, "no CUDA device available; this library has no CPU path");
+    }
+    if (device < 0 || device >= ndev) return fail(F110_ERR_INVALID, "device %d out of range (%d devices)", device, ndev);
+    CK(cudaSetDevice(device));
+    f110_bitmap *b = new f110_bitmap();
+    b->cfg = *cfg;
+    b->device = device;
+    F110BitmapDev &d = b->d;
+    memset(&d, 0, sizeof(d));
+    const int T = cfg->target_beam_count;
+    d.n_beams = cfg->n_beams; d.n_points = T; d.height = cfg->height; d.width = cfg->width;
+    d.wpr = (cfg->width + 31) / 32;
+    d.draw_mode = cfg->draw_mode; d.draw_center = cfg->draw_center; d.scan_is_f32 = cfg->scan_is_f32;
+    d.cx = cfg->height / 2; d.cy = cfg->width / 2;           // lidar.py:79: center = [dims[0] // 2, dims[1] // 2], used as (x, y)
+    d.bg = cfg->bg_white ? 255 : 0; d.fg = cfg->bg_white ? 0 : 255;
+    d.scale = cfg->scaling_factor; d.scale32 = (float)cfg->scaling_factor;
+    const size_t smem = f110_bitmap_smem_bytes(d);
+    if (smem > 200 * 1024) { delete b; return fail(F110_ERR_INVALID, "image too large for the shared-memory rasteriser (%zu bytes)", smem); }
+    size_t bytes = (size_t)T * (4 + 8 + 8) + 16;
+    if (cudaMalloc(&b->tables, bytes) != cudaSuccess) { delete b; return fail(F110_ERR_NOMEM, "cudaMalloc failed"); }
+    double *c = (double *)b->tables, *sn = c + T;
+    int *ix = (int *)(sn + T);
+    cudaMemcpy(c, cos_a, (size_t)T * 8, cudaMemcpyHostToDevice);
+    cudaMemcpy(sn, sin_a, (size_t)T * 8, cudaMemcpyHostToDevice);
+    e = cudaMemcpy(ix, indices, (size_t)T * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { cudaFree(b->tables); delete b; return fail(F110_ERR_CUDA, "table upload failed: %s", cudaGetErrorString(e)); }
+    d.cosa = c; d.sina = sn; d.indices = ix;
+    *out = b;
+    return F110_OK;
+}
+
+extern "C" int f110_bitmap_destroy(f110_bitmap *b)
+{
+    if (!b) return F110_OK;
+    cudaSetDevice(b->device);
+    cudaDeviceSynchronize();
+    if (b->tables) cudaFree(b->tables);
+    delete b;
+    return F110_OK;
+}
+
+extern "C" int f110_bitmap_render(f110_bitmap *b, const void *scans_dev, int64_t n, void *out_dev, int32_t packed, void *stream)
+{
+    if (!b) return fail(F110_ERR_INVALID, "null handle");
+    if (n == 0) return F110_OK;
+    if (!scans_dev || !out_dev || n < 0) return fail(F110_ERR_INVALID, "bad render arguments");
+    CK(cudaSetDevice(b->device));
+    f110_launch_bitmap(b->d, scans_dev, n, (uint8_t *)out_dev, packed, (cudaStream_t)stream);
+    b->launches++;
+    CK(cudaGetLastError());
     return F110_OK;
 }

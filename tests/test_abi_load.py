@@ -54,11 +54,20 @@ def test_no_cpu_fallback():
         BatchF110Env(num_envs=1, num_agents=1, map=os.path.join(MAPS_DIR, "example_map"))
 
 
+def test_no_cpu_fallback_bitmap():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from red_gym_b200 import LidarBitmap
+    with pytest.raises(RuntimeError, match="no CUDA device"):
+        LidarBitmap(num_beams=1080)
+
+
 def test_product_does_not_import_the_oracle():
     """The product path must never route through oracle/ (or any CPU fallback)."""
-    for root in ("red_gym_b200", "f110_gym"):
+    for root in ("red_gym_b200", "f110_gym", "weap_util"):
         for dirpath, _, files in os.walk(os.path.join(REPO, root)):
             for f in files:
                 if f.endswith((".py", ".cu", ".h")):
                     src = open(os.path.join(dirpath, f)).read()
-                    assert "f110_oracle" not in src and "oracle/" not in src, os.path.join(dirpath, f)
+                    assert "f110_oracle" not in src and "oracle/" not in src and "bitmap_oracle" not in src, os.path.join(dirpath, f)
