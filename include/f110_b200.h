@@ -199,6 +199,26 @@ int f110_bitmap_destroy(f110_bitmap *bm);
  * [n][height][ceil(width / 32)] 32-bit words, bit b of word k = pixel 32 k + b, set = drawn colour. */
 int f110_bitmap_render(f110_bitmap *bm, const void *scans_dev, int64_t n, void *out_dev, int32_t packed, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Batched pure-pursuit planner.  Replaces PurePursuitPlanner.plan and its njit helpers
+ * (examples/waypoint_follow.py:15-141,183-217) for n cars at once, on the device.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct f110_pursuit f110_pursuit;
+
+/* wx, wy, wv: host [n_waypoints] = columns wpt_xind, wpt_yind, wpt_vind of the raceline file
+ * (waypoint_follow.py:160-164, config_example_map.yaml); max_reacquire = 20.0 (:153). */
+int f110_pursuit_create(const double *wx, const double *wy, const double *wv, int32_t n_waypoints, double wheelbase,
+                        double max_reacquire, int device, f110_pursuit **out);
+int f110_pursuit_destroy(f110_pursuit *pp);
+/* plan(pose_x, pose_y, pose_theta, lookahead_distance, vgain) (:203-217) for n cars.
+ * x_dev / y_dev / theta_dev: DEVICE, element q at [q * stride] (stride 1 for the rows of f110_buffers.state);
+ * lookahead_dev / vgain_dev: DEVICE [n] per-car values or NULL to use the scalars;
+ * actions_dev: DEVICE [n][2] = (steer, speed), the layout f110_step takes;
+ * picked_dev: DEVICE [n][2] int32 (nearest segment, chosen waypoint index or -2) or NULL. */
+int f110_pursuit_plan(f110_pursuit *pp, const double *x_dev, const double *y_dev, const double *theta_dev, int64_t n,
+                      int64_t stride, double lookahead, double vgain, const double *lookahead_dev, const double *vgain_dev,
+                      double *actions_dev, int32_t *picked_dev, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -14,5 +14,6 @@ _native.load()   # fail loudly when the CUDA library is missing: there is no CPU
 from .batch_env import BatchF110Env   # noqa: E402
 from .host import DEFAULT_PARAMS, MAPS_DIR, MapData   # noqa: E402
 from .lidar_bitmap import LidarBitmap, lidar_to_bitmap   # noqa: E402
+from .pure_pursuit import BatchPurePursuitPlanner   # noqa: E402
 
-__all__ = ["BatchF110Env", "DEFAULT_PARAMS", "MAPS_DIR", "MapData", "LidarBitmap", "lidar_to_bitmap"]
+__all__ = ["BatchF110Env", "DEFAULT_PARAMS", "MAPS_DIR", "MapData", "LidarBitmap", "lidar_to_bitmap", "BatchPurePursuitPlanner"]

@@ -23,7 +23,8 @@ EXPORTS = ["f110_last_error", "f110_abi_version", "f110_device_count", "f110_cre
            "f110_set_map", "f110_set_tables", "f110_set_params", "f110_set_noise_rows", "f110_set_reset_pool",
            "f110_reset", "f110_step", "f110_step_host", "f110_raycast", "f110_get_buffers", "f110_get_config",
            "f110_count_lookups", "f110_enable_timing", "f110_last_raycast_ms", "f110_launch_count", "f110_synchronize",
-           "f110_bitmap_create", "f110_bitmap_destroy", "f110_bitmap_render"]
+           "f110_bitmap_create", "f110_bitmap_destroy", "f110_bitmap_render",
+           "f110_pursuit_create", "f110_pursuit_destroy", "f110_pursuit_plan"]
 BITMAP_MODES = {"FILL": 0, "POLYGON": 1, "RAYS": 2}
 
 
@@ -90,6 +91,9 @@ def load():
     L.f110_bitmap_create.argtypes = [ctypes.POINTER(BitmapConfig), vp, vp, vp, ctypes.c_int, ctypes.POINTER(vp)]
     L.f110_bitmap_destroy.argtypes = [vp]
     L.f110_bitmap_render.argtypes = [vp, vp, i64, vp, i32, vp]
+    L.f110_pursuit_create.argtypes = [vp, vp, vp, i32, f64, f64, ctypes.c_int, ctypes.POINTER(vp)]
+    L.f110_pursuit_destroy.argtypes = [vp]
+    L.f110_pursuit_plan.argtypes = [vp, vp, vp, vp, i64, i64, f64, f64, vp, vp, vp, vp, vp]
     for name in EXPORTS:
         fn = getattr(L, name)
         if name not in ("f110_last_error", "f110_launch_count"):

@@ -10,6 +10,7 @@
 #include "../../include/f110_b200.h"
 #include "f110_dev.h"
 #include "f110_bitmap_dev.h"
+#include "f110_pursuit_dev.h"
 
 static thread_local std::string g_err;
 static int fail(int code, const char *fmt, ...)
@@ -693,6 +694,64 @@ extern "C" int f110_bitmap_render(f110_bitmap *b, const void *scans_dev, int64_t
     CK(cudaSetDevice(b->device));
     f110_launch_bitmap(b->d, scans_dev, n, (uint8_t *)out_dev, packed, (cudaStream_t)stream);
     b->launches++;
+    CK(cudaGetLastError());
+    return F110_OK;
+}
+
+// ---- pure-pursuit planner (f110_pursuit.cu) -----------------------------------------------------------------------
+struct f110_pursuit {
+    int device;
+    F110PursuitDev d;
+    double *tables = nullptr;
+};
+
+extern "C" int f110_pursuit_create(const double *wx, const double *wy, const double *wv, int32_t n, double wheelbase,
+                                   double max_reacquire, int device, f110_pursuit **out)
+{
+    if (!wx || !wy || !wv || !out) return fail(F110_ERR_INVALID, "null argument");
+    if (n < 2 || n > 65536) return fail(F110_ERR_INVALID, "need 2 <= n_waypoints <= 65536");
+    if ((size_t)3 * n * 8 > 200 * 1024) return fail(F110_ERR_INVALID, "raceline too long for the shared-memory planner (%d waypoints)", n);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(F110_ERR_CUDA, "no CUDA device available; this library has no CPU path");
+    }
+    if (device < 0 || device >= ndev) return fail(F110_ERR_INVALID, "device %d out of range (%d devices)", device, ndev);
+    CK(cudaSetDevice(device));
+    f110_pursuit *p = new f110_pursuit();
+    p->device = device;
+    if (cudaMalloc(&p->tables, (size_t)3 * n * 8) != cudaSuccess) { delete p; return fail(F110_ERR_NOMEM, "cudaMalloc failed"); }
+    cudaMemcpy(p->tables, wx, (size_t)n * 8, cudaMemcpyHostToDevice);
+    cudaMemcpy(p->tables + n, wy, (size_t)n * 8, cudaMemcpyHostToDevice);
+    e = cudaMemcpy(p->tables + 2 * (size_t)n, wv, (size_t)n * 8, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { cudaFree(p->tables); delete p; return fail(F110_ERR_CUDA, "waypoint upload failed: %s", cudaGetErrorString(e)); }
+    p->d.n_waypoints = n; p->d.wheelbase = wheelbase; p->d.max_reacquire = max_reacquire;
+    p->d.wx = p->tables; p->d.wy = p->tables + n; p->d.wv = p->tables + 2 * (size_t)n;
+    *out = p;
+    return F110_OK;
+}
+
+extern "C" int f110_pursuit_destroy(f110_pursuit *p)
+{
+    if (!p) return F110_OK;
+    cudaSetDevice(p->device);
+    cudaDeviceSynchronize();
+    if (p->tables) cudaFree(p->tables);
+    delete p;
+    return F110_OK;
+}
+
+extern "C" int f110_pursuit_plan(f110_pursuit *p, const double *x_dev, const double *y_dev, const double *theta_dev, int64_t n,
+                                 int64_t stride, double lookahead, double vgain, const double *lookahead_dev, const double *vgain_dev,
+                                 double *actions_dev, int32_t *picked_dev, void *stream)
+{
+    if (!p) return fail(F110_ERR_INVALID, "null handle");
+    if (n == 0) return F110_OK;
+    if (!x_dev || !y_dev || !theta_dev || !actions_dev || n < 0 || stride < 1) return fail(F110_ERR_INVALID, "bad plan arguments");
+    CK(cudaSetDevice(p->device));
+    f110_launch_pursuit(p->d, x_dev, y_dev, theta_dev, n, stride, lookahead, vgain, lookahead_dev, vgain_dev, actions_dev,
+                        (int *)picked_dev, (cudaStream_t)stream);
     CK(cudaGetLastError());
     return F110_OK;
 }
