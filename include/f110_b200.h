@@ -116,6 +116,14 @@ int f110_destroy(f110_sim *sim);
 int f110_set_map(f110_sim *sim, const double *edt, int32_t h, int32_t w, double resolution,
                  double origin_x, double origin_y, double origin_c, double origin_s, void *stream);
 
+/* The same, with get_dt (laser_models.py:40-53: resolution * scipy.ndimage.distance_transform_edt(bitmap)) done on the
+ * device: free_px is the HOST [h][w] thresholded image (non-zero = free, pixel > 128; row 0 = bottom row), the exact EDT
+ * is built by the library (bit-identical to scipy's).  For update_map / per-episode map randomisation. */
+int f110_set_map_image(f110_sim *sim, const uint8_t *free_px, int32_t h, int32_t w, double resolution,
+                       double origin_x, double origin_y, double origin_c, double origin_s, void *stream);
+/* get_dt alone, device to device: free_dev DEVICE [h][w] bytes -> edt_dev DEVICE [h][w] doubles (metres). */
+int f110_edt_build(const uint8_t *free_dev, int32_t h, int32_t w, double resolution, double *edt_dev, int device, void *stream);
+
 /* Trig tables (laser_models.py:379-381, theta_dis entries) and per-beam tables
  * (base_classes.py:120-156, n_beams entries), computed by the host exactly as the reference does. */
 int f110_set_tables(f110_sim *sim, const double *sines, const double *cosines, const double *scan_angles,

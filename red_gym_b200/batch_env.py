@@ -85,7 +85,7 @@ class BatchF110Env(object):
         if map_data is not None:
             self._upload_map(map_data)
         else:
-            self._upload_map(host.MapData(self.map_path, self.map_ext))
+            self._upload_map(host.MapData(self.map_path, self.map_ext, edt=kwargs.get("edt", "scipy")))
         if self.noise == "numpy":
             self._ensure_noise(64)
         if reset_poses is not None:
@@ -98,8 +98,12 @@ class BatchF110Env(object):
 
     def _upload_map(self, m):
         self.map = m
-        nat.check(self.lib.f110_set_map(self._h, _hp(m.edt), m.height, m.width, m.resolution, m.origin[0], m.origin[1],
-                                        m.orig_c, m.orig_s, None))
+        if m.edt is None:      # thresholded image only: get_dt runs on the device (csrc/f110_edt.cu)
+            nat.check(self.lib.f110_set_map_image(self._h, _hp(m.free), m.height, m.width, m.resolution, m.origin[0], m.origin[1],
+                                                  m.orig_c, m.orig_s, None))
+        else:
+            nat.check(self.lib.f110_set_map(self._h, _hp(m.edt), m.height, m.width, m.resolution, m.origin[0], m.origin[1],
+                                            m.orig_c, m.orig_s, None))
 
     def _ensure_noise(self, rows):
         if self.noise != "numpy" or rows <= self._noise_rows:
@@ -145,9 +149,10 @@ class BatchF110Env(object):
         nat.check(self.lib.f110_set_reset_pool(self._h, _hp(poses), poses.shape[0], None))
 
     # ------------------------------------------------------------------ reference API (batched)
-    def update_map(self, map_path, map_ext):
-        """F110Env.update_map (f110_env.py:349-360): map_path is the yaml path."""
-        self._upload_map(host.MapData(map_path, map_ext))
+    def update_map(self, map_path, map_ext, edt="gpu"):
+        """F110Env.update_map (f110_env.py:349-360): map_path is the yaml path.  The EDT (get_dt) is built on the device by
+        default (bit-identical to scipy's, milliseconds instead of seconds); edt='scipy' does it on the host."""
+        self._upload_map(host.MapData(map_path, map_ext, edt=edt))
 
     def update_params(self, params, index=-1):
         """F110Env.update_params -> Simulator.update_params (f110_env.py:362, base_classes.py:507-527)."""

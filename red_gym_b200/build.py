@@ -20,6 +20,7 @@ UNITS = [
     ("f110_order.cu", []),
     ("f110_bitmap.cu", ["-fmad=false"]),
     ("f110_pursuit.cu", ["-fmad=false"]),
+    ("f110_edt.cu", ["-fmad=false"]),
     ("f110_abi.cu", []),
 ]
 

@@ -232,10 +232,14 @@ extern "C" int f110_destroy(f110_sim *s)
     return F110_OK;
 }
 
-extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w, double res, double ox, double oy,
-                            double oc, double os, void *stream)
+void f110_launch_edt_build(const uint8_t *free_px, unsigned *scratch_g, double *edt, int h, int w, double res, cudaStream_t st);
+
+// edt: host [h][w] metres, or null with free_px: host [h][w] bytes (non-zero = free) to build the EDT on the device
+static int set_map_impl(f110_sim *s, const double *edt, const uint8_t *free_px, int32_t h, int32_t w, double res, double ox,
+                        double oy, double oc, double os, void *stream)
 {
-    if (!s || !edt || h < 1 || w < 1 || !(res > 0)) return fail(F110_ERR_INVALID, "bad map arguments");
+    if (!s || (!edt && !free_px) || h < 1 || w < 1 || !(res > 0)) return fail(F110_ERR_INVALID, "bad map arguments");
+    if (free_px && (h > 65534 || w > 65534)) return fail(F110_ERR_INVALID, "map too large for the device EDT");
     cudaStream_t st = (cudaStream_t)stream;
     CK(cudaSetDevice(s->device));
     CK(cudaStreamSynchronize(st));
@@ -248,19 +252,35 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
     if (cells >= (1ull << 31)) return fail(F110_ERR_INVALID, "map too large");
     CK(cudaMalloc(&s->edt64, cells * 8));
     CK(cudaMalloc(&s->edt32, cells * 4));
-    CK(cudaMemcpyAsync(s->edt64, edt, cells * 8, cudaMemcpyHostToDevice, st));
+    double last_cell;
+    if (edt) {
+        CK(cudaMemcpyAsync(s->edt64, edt, cells * 8, cudaMemcpyHostToDevice, st));
+        last_cell = edt[cells - 1];
+    } else {
+        uint8_t *fp = nullptr;
+        unsigned *g = nullptr;
+        CK(cudaMalloc(&fp, cells));
+        if (cudaMalloc(&g, cells * 4) != cudaSuccess) { cudaFree(fp); return fail(F110_ERR_NOMEM, "cudaMalloc failed"); }
+        cudaMemcpyAsync(fp, free_px, cells, cudaMemcpyHostToDevice, st);
+        f110_launch_edt_build(fp, g, s->edt64, h, w, res, st);
+        s->launches += 2;
+        cudaError_t e1 = cudaMemcpyAsync(&last_cell, s->edt64 + cells - 1, 8, cudaMemcpyDeviceToHost, st);
+        cudaError_t e2 = cudaStreamSynchronize(st);
+        cudaFree(fp); cudaFree(g);
+        if (e1 != cudaSuccess || e2 != cudaSuccess) return fail(F110_ERR_CUDA, "device EDT failed: %s", cudaGetErrorString(e2 != cudaSuccess ? e2 : e1));
+    }
     d.map_h = h; d.map_w = w; d.res = res; d.inv_res = 1.0 / res; d.ox = ox; d.oy = oy; d.oc = oc; d.os = os;
     d.xmax = w * res; d.ymax = h * res;   // width * resolution, height * resolution (laser_models.py:79)
     int ex;
     d.res_pow2 = (frexp(res, &ex) == 0.5);
     d.has_rot = !(oc == 1.0 && os == 0.0);
     d.max_c32 = (float)(s->cfg.max_range / res); d.res32 = (float)res;
-    d.oob64 = edt[cells - 1];             // dt[-1, -1]
+    d.oob64 = last_cell;                  // dt[-1, -1]
     // fp32 encoding: free cells min(dist, cap), obstacle cells `sent`, max_range < cap < sent (all in cells)
     const float cap = floorf(d.max_c32) + 2.0f;
     d.sent32 = 1024.0f;
     while (d.sent32 <= cap) d.sent32 *= 2.0f;
-    d.oob32 = edt[cells - 1] > s->cfg.eps ? fminf((float)(edt[cells - 1] / res), cap) : d.sent32;
+    d.oob32 = last_cell > s->cfg.eps ? fminf((float)(last_cell / res), cap) : d.sent32;
     d.edt64 = s->edt64; d.edt32 = s->edt32;
     f110_launch_edt32(s->edt64, s->edt32, cells, d.inv_res, s->cfg.eps, cap, d.sent32, st);
     s->launches += 1;
@@ -327,6 +347,40 @@ extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w
         CK(cudaMemcpy(s->dir32, dir.data(), dir.size() * sizeof(float4), cudaMemcpyHostToDevice));
         CK(cudaMemcpy(s->dir2, dir2.data(), dir2.size() * sizeof(float2), cudaMemcpyHostToDevice));
     }
+    return F110_OK;
+}
+
+extern "C" int f110_set_map(f110_sim *s, const double *edt, int32_t h, int32_t w, double res, double ox, double oy,
+                            double oc, double os, void *stream)
+{
+    if (!edt) return fail(F110_ERR_INVALID, "bad map arguments");
+    return set_map_impl(s, edt, nullptr, h, w, res, ox, oy, oc, os, stream);
+}
+
+extern "C" int f110_set_map_image(f110_sim *s, const uint8_t *free_px, int32_t h, int32_t w, double res, double ox, double oy,
+                                  double oc, double os, void *stream)
+{
+    if (!free_px) return fail(F110_ERR_INVALID, "bad map arguments");
+    return set_map_impl(s, nullptr, free_px, h, w, res, ox, oy, oc, os, stream);
+}
+
+extern "C" int f110_edt_build(const uint8_t *free_dev, int32_t h, int32_t w, double res, double *edt_dev, int device, void *stream)
+{
+    if (!free_dev || !edt_dev || h < 1 || w < 1 || h > 65534 || w > 65534 || !(res > 0)) return fail(F110_ERR_INVALID, "bad EDT arguments");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(F110_ERR_CUDA, "no CUDA device available; this library has no CPU path");
+    }
+    if (device < 0 || device >= ndev) return fail(F110_ERR_INVALID, "device %d out of range (%d devices)", device, ndev);
+    CK(cudaSetDevice(device));
+    unsigned *g = nullptr;
+    if (cudaMalloc(&g, (size_t)h * w * 4) != cudaSuccess) return fail(F110_ERR_NOMEM, "cudaMalloc failed");
+    f110_launch_edt_build(free_dev, g, edt_dev, h, w, res, (cudaStream_t)stream);
+    cudaError_t e = cudaGetLastError();
+    cudaError_t e2 = cudaStreamSynchronize((cudaStream_t)stream);      // the scratch buffer is freed on return
+    cudaFree(g);
+    if (e != cudaSuccess || e2 != cudaSuccess) return fail(F110_ERR_CUDA, "EDT kernels failed: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
     return F110_OK;
 }
 

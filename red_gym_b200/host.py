@@ -32,13 +32,15 @@ def resolve_map(map_name):
 class MapData(object):
     """Occupancy image -> metric EDT (ScanSimulator2D.set_map, laser_models.py:383-427)."""
 
-    def __init__(self, map_path, map_ext):
+    def __init__(self, map_path, map_ext, edt="scipy"):
+        """edt='scipy': get_dt on the host like the reference; edt='gpu': keep only the thresholded image, the library
+        builds the (bit-identical) EDT on the device when the map is uploaded (f110_set_map_image)."""
         import yaml
         from PIL import Image
-        from scipy.ndimage import distance_transform_edt
         img_path = os.path.splitext(map_path)[0] + map_ext
         occ = np.asarray(Image.open(img_path).transpose(Image.FLIP_TOP_BOTTOM), dtype=np.float64)
         free = occ > 128.0                                   # <=128 -> obstacle, >128 -> free (:403-404)
+        self.free = np.ascontiguousarray(free, dtype=np.uint8)
         with open(map_path, "r") as stream:
             meta = yaml.safe_load(stream)
         self.resolution = float(meta["resolution"])
@@ -48,13 +50,35 @@ class MapData(object):
         self.orig_s = float(np.sin(origin[2]))
         self.height, self.width = occ.shape[0], occ.shape[1]
         # get_dt (laser_models.py:40-53): exact Euclidean distance to the nearest obstacle pixel, metres
-        self.edt = np.ascontiguousarray(self.resolution * distance_transform_edt(free))
+        if edt == "scipy":
+            from scipy.ndimage import distance_transform_edt
+            self.edt = np.ascontiguousarray(self.resolution * distance_transform_edt(free))
+        elif edt == "gpu":
+            self.edt = None
+        else:
+            raise ValueError("edt must be 'scipy' or 'gpu'")
         self.path = map_path
         self.ext = map_ext
 
     @classmethod
+    def from_free_mask(cls, free, resolution, origin=(0.0, 0.0, 0.0)):
+        """A map given as its thresholded image (non-zero = free, row 0 = bottom); the EDT is built on the device."""
+        self = cls.__new__(cls)
+        self.free = np.ascontiguousarray(np.asarray(free) != 0, dtype=np.uint8)
+        self.edt = None
+        self.height, self.width = self.free.shape
+        self.resolution = float(resolution)
+        self.origin = tuple(float(o) for o in origin)
+        self.orig_c = float(np.cos(origin[2]))
+        self.orig_s = float(np.sin(origin[2]))
+        self.path = None
+        self.ext = None
+        return self
+
+    @classmethod
     def from_arrays(cls, edt, resolution, origin=(0.0, 0.0, 0.0)):
         self = cls.__new__(cls)
+        self.free = None
         self.edt = np.ascontiguousarray(edt, dtype=np.float64)
         self.height, self.width = self.edt.shape
         self.resolution = float(resolution)
@@ -160,3 +184,19 @@ def free_space_poses(m, n, seed=7, clearance=0.3):
     x = m.origin[0] + gx * m.orig_c - gy * m.orig_s
     y = m.origin[1] + gx * m.orig_s + gy * m.orig_c
     return np.stack([x, y, rng.uniform(0, 2 * np.pi, n)], axis=1)
+
+
+def gpu_edt(free, resolution, device=0):
+    """get_dt (laser_models.py:40-53) on the device: free = (h, w) array/tensor, non-zero = free space.
+    Returns a (h, w) float64 CUDA tensor equal to resolution * scipy.ndimage.distance_transform_edt(free)."""
+    import ctypes
+    import torch
+    from . import _native as nat
+    dev = torch.device("cuda", int(device))
+    f = (torch.as_tensor(free, device=dev) != 0).to(torch.uint8).contiguous()
+    h, w = f.shape
+    out = torch.empty((h, w), dtype=torch.float64, device=dev)
+    stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    nat.check(nat.load().f110_edt_build(ctypes.c_void_p(f.data_ptr()), h, w, float(resolution), ctypes.c_void_p(out.data_ptr()),
+                                        int(device), stream))
+    return out
