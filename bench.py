@@ -352,6 +352,78 @@ def run_sweep(args):
         dist.destroy_process_group()
 
 
+def run_downstream(args):
+    """The two device-side neighbours of the step: scan -> 256x256 bitmap (FILL, the call src/SAL.py makes
+    every step) and the pure-pursuit planner, timed on the scans / poses of a stepped env.  One JSON line."""
+    import torch
+    from red_gym_b200 import BatchF110Env, BatchPurePursuitPlanner, LidarBitmap, MAPS_DIR
+    from argparse import Namespace
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    n = args.envs or 65536
+    K, W = max(args.steps, 1), max(args.warmup, 3)
+    env = BatchF110Env(num_envs=n, device=local, dtype="fp32", noise="philox", num_agents=1, map=os.path.join(MAPS_DIR, "example_map"))
+    env.reset(make_poses(n, 1))
+    bank = action_bank(torch, n, 1, device, 2, 2024)
+    for i in range(20):
+        env.step(bank[i % 2])
+    scans = env.scans.view(n, 1080)
+    peak, peak_src = load_peaks()
+    res = {}
+
+    def timeit(fn):
+        for _ in range(W):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(K):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / K
+
+    bm = LidarBitmap(num_beams=1080, draw_mode="FILL", bg_color="black", scan_dtype="fp32", device=local)
+    out = torch.empty((n, 256, 256), dtype=torch.uint8, device=device)
+    ms = timeit(lambda: bm(scans, out=out))
+    by = n * (256 * 256 + 600 * 4)            # algorithmic bytes: the image written + the 600 sampled ranges read
+    res["bitmap_u8"] = {"ms": ms, "images_per_s": n / (ms * 1e-3), "algorithmic_GBps": by / (ms * 1e-3) / 1e9,
+                        "frac_of_hbm_peak": by / (ms * 1e-3) / 1e9 / peak, "bytes_per_image": by // n}
+    outp = torch.empty((n, 256, 8), dtype=torch.int32, device=device)
+    ms = timeit(lambda: bm(scans, out=outp, packed=True))
+    by = n * (256 * 32 + 600 * 4)
+    res["bitmap_packed"] = {"ms": ms, "images_per_s": n / (ms * 1e-3), "algorithmic_GBps": by / (ms * 1e-3) / 1e9,
+                            "frac_of_hbm_peak": by / (ms * 1e-3) / 1e9 / peak, "bytes_per_image": by // n}
+    conf = Namespace(wpt_path=os.path.join(MAPS_DIR, "example_waypoints.csv"), wpt_delim=";", wpt_rowskip=3, wpt_xind=1, wpt_yind=2, wpt_vind=5)
+    pl = BatchPurePursuitPlanner(conf, 0.17145 + 0.15875, device=local)
+    act = torch.empty((n, 1, 2), dtype=torch.float64, device=device)
+    ms = timeit(lambda: pl.plan_actions(env, 0.82461887897713965, 1.375, out=act))
+    res["pure_pursuit"] = {"ms": ms, "plans_per_s": n / (ms * 1e-3), "segments_per_plan": 782}
+    cpu = None
+    if not args.no_cpu:
+        sys.path.insert(0, os.path.join(REPO, "oracle"))
+        import bitmap_oracle as bo
+        import pursuit_oracle as po
+        sc = scans[:64].cpu().numpy()
+        t0 = time.perf_counter(); k = 0
+        while time.perf_counter() - t0 < 8.0 and k < 64:
+            bo.lidar_to_bitmap(sc[k], draw_mode="FILL", bg_color="black"); k += 1
+        tb = (time.perf_counter() - t0) / k
+        wp = po.load_waypoints(conf.wpt_path)
+        st = env.state.cpu().numpy()
+        t0 = time.perf_counter(); j = 0
+        while time.perf_counter() - t0 < 4.0 and j < 2000:
+            po.plan(wp, st[0, j, 0], st[1, j, 0], st[4, j, 0], 0.82461887897713965, 1.375, 0.3302); j += 1
+        tp = (time.perf_counter() - t0) / j
+        cpu = {"kind": "port", "cores": 1, "bitmap_images_per_s": 1.0 / tb, "pursuit_plans_per_s": 1.0 / tp,
+               "sample": "%d images / %d plans with the pure-Python + numpy oracle (the reference uses OpenCV / Numba)" % (k, j)}
+    print(json.dumps({"metric": "images/s (scan -> 256x256 bitmap, FILL)", "value": res["bitmap_u8"]["images_per_s"], "unit": "images/s",
+                      "n_gpus": 1, "steps": K, "warmup": W, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+                      "data": "synthetic", "config": {"workload": "downstream", "scans": n, "beams": 1080, "target_beam_count": 600},
+                      "hbm_peak_GBps": peak, "peak_source": peak_src, "downstream": res, "cpu_baseline": cpu}))
+
+
 def cpu_reference(workload, seconds=12.0, nthreads=0):
     """The CPU restatement of the reference (oracle/, pthreads over envs) on a bounded sample of the workload."""
     sys.path.insert(0, os.path.join(REPO, "oracle"))
@@ -404,7 +476,7 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS) + ["config5"])
+    ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS) + ["config5", "downstream"])
     ap.add_argument("--sweep-sizes", default="1024,2048,4096")
     ap.add_argument("--sweep-beams", default="270,1080,2160")
     ap.add_argument("--envs", type=int, default=0, help="override envs per GPU")
@@ -421,6 +493,11 @@ def main():
             print(json.dumps({"impl": "reference", "unavailable": "the sweep is a GPU-only diagnostic; use --workload config3"}))
         else:
             run_sweep(args)
+    elif args.workload == "downstream":
+        if args.impl == "reference":
+            print(json.dumps({"impl": "reference", "unavailable": "diagnostic workload; use --workload config3"}))
+        else:
+            run_downstream(args)
     elif args.impl == "reference":
         run_reference(args)
     else:

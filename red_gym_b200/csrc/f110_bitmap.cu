@@ -63,26 +63,39 @@ static __device__ __forceinline__ void set_px(unsigned *mask, int wpr, int x, in
     atomicOr(mask + y * wpr + (x >> 5), 1u << (x & 31));
 }
 
-// cv::Line(img, p1, p2, color, LINE_8), thickness 1
-static __device__ void draw_line(unsigned *mask, int wpr, int w, int h, int ax, int ay, int bx, int by)
+// cv::Line(img, p1, p2, color, LINE_8), thickness 1, split in two so that a long line can be drawn by a whole warp:
+// line_setup clips and normalises (left to right, major axis first), line_span draws pixels [i0, i1) of it.
+struct LineJob { int px, py, dx, dy, sy; bool vert; };
+
+static __device__ __forceinline__ bool line_setup(int w, int h, int ax, int ay, int bx, int by, LineJob &j)
 {
     long long x1 = ax, y1 = ay, x2 = bx, y2 = by;
     if ((unsigned)ax >= (unsigned)w || (unsigned)bx >= (unsigned)w || (unsigned)ay >= (unsigned)h || (unsigned)by >= (unsigned)h)
-        if (!clip_line(w, h, x1, y1, x2, y2)) return;
-    int dx = (int)(x2 - x1), dy = (int)(y2 - y1), sy = 1;
-    int px = (int)x1, py = (int)y1;
-    if (dx < 0) { dx = -dx; dy = -dy; px = (int)x2; py = (int)y2; }       // left to right
-    if (dy < 0) { dy = -dy; sy = -1; }
-    const bool vert = dy > dx;
-    if (vert) { int t = dx; dx = dy; dy = t; }
-    // LineIterator: the minor coordinate advances when err < 0; err starts at dx - 2 dy, loses 2 dy per step and
-    // gains 2 dx per minor step
-    int err = dx - 2 * dy, m = 0;
-    for (int i = 0; i <= dx; i++) {
-        if (vert) set_px(mask, wpr, px + m, py + sy * i);
-        else set_px(mask, wpr, px + i, py + sy * m);
+        if (!clip_line(w, h, x1, y1, x2, y2)) return false;
+    int dx = (int)(x2 - x1), dy = (int)(y2 - y1);
+    j.sy = 1;
+    j.px = (int)x1; j.py = (int)y1;
+    if (dx < 0) { dx = -dx; dy = -dy; j.px = (int)x2; j.py = (int)y2; }       // left to right
+    if (dy < 0) { dy = -dy; j.sy = -1; }
+    j.vert = dy > dx;
+    if (j.vert) { int t = dx; dx = dy; dy = t; }
+    j.dx = dx; j.dy = dy;
+    return true;
+}
+
+// LineIterator: the minor coordinate advances when err < 0; err starts at dx - 2 dy, loses 2 dy per step and gains 2 dx
+// per minor step, so before pixel i the minor offset is m_i = floor((2 dy i + dx - 1) / (2 dx)) and
+// err_i = dx - 2 dy (i + 1) + 2 dx m_i: a span can start anywhere.
+static __device__ __forceinline__ void line_span(unsigned *mask, int wpr, const LineJob &j, int i0, int i1)
+{
+    if (i0 >= i1) return;
+    int m = (i0 > 0 && j.dx > 0) ? (int)((2ll * j.dy * i0 + j.dx - 1) / (2ll * j.dx)) : 0;
+    int err = j.dx - 2 * j.dy * (i0 + 1) + 2 * j.dx * m;
+    for (int i = i0; i < i1; i++) {
+        if (j.vert) set_px(mask, wpr, j.px + m, j.py + j.sy * i);
+        else set_px(mask, wpr, j.px + i, j.py + j.sy * m);
         const bool neg = err < 0;
-        err += -2 * dy + (neg ? 2 * dx : 0);
+        err += -2 * j.dy + (neg ? 2 * j.dx : 0);
         m += neg ? 1 : 0;
     }
 }
@@ -97,12 +110,14 @@ static __device__ void fill_box(unsigned *mask, int wpr, int w, int h, int cx, i
         }
 }
 
-// One polygon edge p0 -> p1 for the scan-line fill (cv::CollectPolyEdges + the per-row part of FillEdgeCollection):
-// toggles the parity bit right of the edge in every row it crosses
-static __device__ void fill_edge(unsigned *par, unsigned *exact, unsigned *carry, int wpr, int w, int h,
-                                 int p0x, int p0y, int p1x, int p1y)
+// One polygon edge p0 -> p1 of the scan-line fill (cv::CollectPolyEdges + the per-row part of FillEdgeCollection), also
+// split: edge_setup gives the 16.16 fixed-point x at row ya and the slope, edge_rows toggles the parity bit right of the
+// edge in rows [y0, y1).
+struct EdgeJob { int ya, yb; long long x, dx; };
+
+static __device__ __forceinline__ bool edge_setup(int w, int h, int p0x, int p0y, int p1x, int p1y, EdgeJob &e)
 {
-    if (p0y == p1y) return;
+    if (p0y == p1y) return false;
     long long c0x = p0x, c0y = p0y, c1x = p1x, c1y = p1y;
     if ((unsigned)p0x >= (unsigned)w || (unsigned)p1x >= (unsigned)w || (unsigned)p0y >= (unsigned)h || (unsigned)p1y >= (unsigned)h) {
         long long q0x = p0x, q0y = p0y, q1x = p1x, q1y = p1y;
@@ -110,14 +125,21 @@ static __device__ void fill_edge(unsigned *par, unsigned *exact, unsigned *carry
         c0x = q0x; c1x = q1x;                                   // x always from the clipped end points,
         if (q0y != q1y) { c0y = q0y; c1y = q1y; }               // y only when the clipped piece spans rows
     }
-    const long long dx = ((c1x - c0x) * XY_ONE) / (c1y - c0y);      // C division: truncates, like the reference
+    e.dx = ((c1x - c0x) * XY_ONE) / (c1y - c0y);                // C division: truncates, like the reference
     int y0, y1;
     long long x;
-    if (p0y < p1y) { y0 = p0y; y1 = p1y; x = c0x * XY_ONE + (p0y - c0y) * dx; }
-    else { y0 = p1y; y1 = p0y; x = c1x * XY_ONE + (p1y - c1y) * dx; }
-    const int ya = max(y0, 0), yb = min(y1, h);
-    x += (long long)(ya - y0) * dx;
-    for (int y = ya; y < yb; y++, x += dx) {
+    if (p0y < p1y) { y0 = p0y; y1 = p1y; x = c0x * XY_ONE + (p0y - c0y) * e.dx; }
+    else { y0 = p1y; y1 = p0y; x = c1x * XY_ONE + (p1y - c1y) * e.dx; }
+    e.ya = max(y0, 0); e.yb = min(y1, h);
+    e.x = x + (long long)(e.ya - y0) * e.dx;
+    return e.ya < e.yb;
+}
+
+static __device__ __forceinline__ void edge_rows(unsigned *par, unsigned *exact, unsigned *carry, int wpr, int w, const EdgeJob &e,
+                                                 int y0, int y1)
+{
+    long long x = e.x + (long long)(y0 - e.ya) * e.dx;
+    for (int y = y0; y < y1; y++, x += e.dx) {
         const long long a = x >> XY_SHIFT;
         if (a < 0) atomicXor(carry + y, 1u);
         else if (a < w) {
@@ -127,8 +149,13 @@ static __device__ void fill_edge(unsigned *par, unsigned *exact, unsigned *carry
     }
 }
 
-// dynamic shared memory: pts[n_points] (int2) | mask | par | exact (height * wpr words each) | carry[height]
-__global__ void __launch_bounds__(256) k_lidar_bitmap(const F110BitmapDev d, const void *__restrict__ scans, long long n,
+// Items longer than this many pixels / rows are not finished by the thread that owns them (the other 255 threads of the
+// CTA would wait at the barrier) but queued and drawn by whole warps, 32 pixels / rows at a time.
+#define BM_SHORT 12
+
+// dynamic shared memory: pts[n_points] (int2) | mask | par | exact (height * wpr words each) | carry[height] |
+// queue[2 * n_points] | queue counter (4 words) | colour table (256 x 8 bytes)
+__global__ void __launch_bounds__(256, 4) k_lidar_bitmap(const F110BitmapDev d, const void *__restrict__ scans, long long n,
                                                       uint8_t *__restrict__ out, int packed)
 {
     extern __shared__ unsigned smem[];
@@ -138,7 +165,16 @@ __global__ void __launch_bounds__(256) k_lidar_bitmap(const F110BitmapDev d, con
     unsigned *par = mask + H * wpr;
     unsigned *exact = par + H * wpr;
     unsigned *carry = exact + H * wpr;
-    const int tid = threadIdx.x, nt = blockDim.x;
+    unsigned *queue = carry + H;              // entries: point index t, bit 31 set = fill edge (else line)
+    unsigned *qn = queue + 2 * T;
+    uint2 *lut = (uint2 *)(smem + ((2 * T + 3 * H * wpr + H + 2 * T + 4 + 1) & ~1));   // 256 entries: 8 mask bits -> 8 bytes of bg / fg
+    const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, wid = tid >> 5, nw = nt >> 5;
+    const bool rays = d.draw_mode == F110_BM_RAYS, fill = d.draw_mode == F110_BM_FILL;
+    for (int b = tid; b < 256; b += nt) {
+        const unsigned bg = d.bg * 0x01010101u, fx = (d.fg ^ d.bg) * 0x01010101u;
+        const unsigned m0 = (((b & 15u) * 0x00204081u) & 0x01010101u) * 0xffu, m1 = ((((b >> 4) & 15u) * 0x00204081u) & 0x01010101u) * 0xffu;
+        lut[b] = make_uint2(bg ^ (fx & m0), bg ^ (fx & m1));
+    }
     for (long long img = blockIdx.x; img < n; img += gridDim.x) {
         // polar -> pixel (lidar.py:71-83): rint(c + (scaling_factor * data) * cos(angle))
         for (int t = tid; t < T; t += nt) {
@@ -149,21 +185,49 @@ __global__ void __launch_bounds__(256) k_lidar_bitmap(const F110BitmapDev d, con
             pts[t] = make_int2((int)rint((double)d.cx + sd * d.cosa[t]), (int)rint((double)d.cy + sd * d.sina[t]));
         }
         for (int i = tid; i < 3 * H * wpr + H; i += nt) mask[i] = 0u;
+        if (tid == 0) *qn = 0u;
         __syncthreads();
-        if (d.draw_mode == F110_BM_RAYS) {
-            for (int t = tid; t < T; t += nt) {
-                draw_line(mask, wpr, W, H, d.cx, d.cy, pts[t].x, pts[t].y);
-                fill_box(mask, wpr, W, H, pts[t].x, pts[t].y, true);
+        // pass 1: one thread per line / edge; short ones are finished here, long ones queued
+        for (int t = tid; t < T; t += nt) {
+            const int2 p1 = pts[t];
+            const int2 p0 = rays ? make_int2(d.cx, d.cy) : pts[t ? t - 1 : T - 1];
+            LineJob lj;
+            if (line_setup(W, H, p0.x, p0.y, p1.x, p1.y, lj)) {
+                if (lj.dx < BM_SHORT) line_span(mask, wpr, lj, 0, lj.dx + 1);
+                else queue[atomicAdd(qn, 1u)] = (unsigned)t;
             }
-        } else {
-            for (int t = tid; t < T; t += nt) {
-                const int2 p0 = pts[t ? t - 1 : T - 1], p1 = pts[t];
-                draw_line(mask, wpr, W, H, p0.x, p0.y, p1.x, p1.y);
-                if (d.draw_mode == F110_BM_FILL) fill_edge(par, exact, carry, wpr, W, H, p0.x, p0.y, p1.x, p1.y);
+            if (rays) fill_box(mask, wpr, W, H, p1.x, p1.y, true);
+            if (fill) {
+                EdgeJob ej;
+                if (edge_setup(W, H, p0.x, p0.y, p1.x, p1.y, ej)) {
+                    if (ej.yb - ej.ya <= BM_SHORT) edge_rows(par, exact, carry, wpr, W, ej, ej.ya, ej.yb);
+                    else queue[atomicAdd(qn, 1u)] = (unsigned)t | 0x80000000u;
+                }
             }
         }
         __syncthreads();
-        if (d.draw_mode == F110_BM_FILL) {
+        // pass 2: the queued long items, one warp per item, lanes over pixels / rows
+        const int nq = (int)*qn;
+        for (int k = wid; k < nq; k += nw) {
+            const unsigned e = queue[k];
+            const int t = (int)(e & 0x7fffffffu);
+            const int2 p1 = pts[t];
+            const int2 p0 = rays ? make_int2(d.cx, d.cy) : pts[t ? t - 1 : T - 1];
+            if (e & 0x80000000u) {
+                EdgeJob ej;
+                edge_setup(W, H, p0.x, p0.y, p1.x, p1.y, ej);
+                const int rows = ej.yb - ej.ya, per = (rows + 31) >> 5;
+                const int y0 = ej.ya + lane * per;
+                edge_rows(par, exact, carry, wpr, W, ej, min(y0, ej.yb), min(y0 + per, ej.yb));
+            } else {
+                LineJob lj;
+                line_setup(W, H, p0.x, p0.y, p1.x, p1.y, lj);
+                const int per = (lj.dx + 1 + 31) >> 5;
+                line_span(mask, wpr, lj, min(lane * per, lj.dx + 1), min(lane * per + per, lj.dx + 1));
+            }
+        }
+        __syncthreads();
+        if (fill) {
             // per row: inclusive prefix XOR of the toggles (a toggle sits one pixel right of its edge)
             for (int y = tid; y < H; y += nt) {
                 unsigned c = (carry[y] & 1u) ? 0xffffffffu : 0u;
@@ -177,42 +241,33 @@ __global__ void __launch_bounds__(256) k_lidar_bitmap(const F110BitmapDev d, con
             }
             __syncthreads();
         }
-        if (d.draw_center && tid == 0) fill_box(mask, wpr, W, H, d.cx, d.cy, d.draw_mode != F110_BM_FILL);
+        if (d.draw_center && tid < 25) {      // cv2.rectangle(center - 2, center + 2, thickness = -1): 5 x 5 pixels
+            const int x = d.cx - 2 + tid % 5, y = d.cy - 2 + tid / 5;
+            if ((unsigned)x < (unsigned)W && (unsigned)y < (unsigned)H) {
+                if (!fill) atomicOr(mask + y * wpr + (x >> 5), 1u << (x & 31));
+                else atomicAnd(mask + y * wpr + (x >> 5), ~(1u << (x & 31)));
+            }
+        }
         __syncthreads();
         if (packed) {
             // 1 bit per pixel, row-major, bit b of word k of a row = pixel 32 k + b (set = drawn)
             unsigned *o = (unsigned *)out + (size_t)img * H * wpr;
-            for (int i = tid; i < H * wpr; i += nt) {
-                unsigned v = mask[i];
-                const int k = i % wpr;
-                if (k == wpr - 1 && (W & 31)) v &= (1u << (W & 31)) - 1u;
-                o[i] = v;
-            }
-        } else if ((W & 15) == 0) {
+            const unsigned last = (W & 31) ? (1u << (W & 31)) - 1u : 0xffffffffu;
+            for (int i = tid; i < H * wpr; i += nt) o[i] = ((i + 1) % wpr == 0) ? (mask[i] & last) : mask[i];
+        } else if ((W & 31) == 0) {
+            // one mask word -> 32 pixels -> two 16-byte stores; byte -> 8 colour bytes through the table
             uint4 *o = (uint4 *)(out + (size_t)img * H * W);
-            const unsigned fg = d.fg * 0x01010101u, bg = d.bg * 0x01010101u;
-            for (int i = tid; i < H * (W >> 4); i += nt) {
-                const int y = i / (W >> 4), g = i % (W >> 4);
-                const unsigned bits = (mask[y * wpr + (g >> 1)] >> ((g & 1) * 16)) & 0xffffu;
-                uint4 v;
-                unsigned q[4];
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const unsigned b4 = (bits >> (4 * j)) & 15u;
-                    // spread 4 bits to 4 byte lanes of 0x00 / 0xff
-                    unsigned m = ((b4 & 1u) ? 0x000000ffu : 0u) | ((b4 & 2u) ? 0x0000ff00u : 0u) |
-                                 ((b4 & 4u) ? 0x00ff0000u : 0u) | ((b4 & 8u) ? 0xff000000u : 0u);
-                    q[j] = (fg & m) | (bg & ~m);
-                }
-                v.x = q[0]; v.y = q[1]; v.z = q[2]; v.w = q[3];
-                o[i] = v;
+            for (int i = tid; i < H * wpr; i += nt) {
+                const unsigned v = mask[i];
+                const uint2 a0 = lut[v & 255u], a1 = lut[(v >> 8) & 255u], a2 = lut[(v >> 16) & 255u], a3 = lut[v >> 24];
+                o[2 * i] = make_uint4(a0.x, a0.y, a1.x, a1.y);
+                o[2 * i + 1] = make_uint4(a2.x, a2.y, a3.x, a3.y);
             }
         } else {
             uint8_t *o = out + (size_t)img * H * W;
-            for (int i = tid; i < H * W; i += nt) {
-                const int y = i / W, x = i % W;
-                o[i] = ((mask[y * wpr + (x >> 5)] >> (x & 31)) & 1u) ? d.fg : d.bg;
-            }
+            for (int y = wid; y < H; y += nw)
+                for (int x = lane; x < W; x += 32)
+                    o[(size_t)y * W + x] = ((mask[y * wpr + (x >> 5)] >> (x & 31)) & 1u) ? d.fg : d.bg;
         }
         __syncthreads();
     }
@@ -220,7 +275,7 @@ __global__ void __launch_bounds__(256) k_lidar_bitmap(const F110BitmapDev d, con
 
 size_t f110_bitmap_smem_bytes(const F110BitmapDev &d)
 {
-    return (size_t)4 * (2 * (size_t)d.n_points + 3 * (size_t)d.height * d.wpr + d.height);
+    return (size_t)4 * (2 * (size_t)d.n_points + 3 * (size_t)d.height * d.wpr + d.height + 2 * (size_t)d.n_points + 4 + 2 + 512);
 }
 
 void f110_launch_bitmap(const F110BitmapDev &d, const void *scans, long long n, uint8_t *out, int packed, cudaStream_t st)
