@@ -110,5 +110,9 @@ class F110Env(_Base):
 
     def render(self, mode='human'):
         """The reference draws with pyglet/OpenGL (f110_env.py:385-416) -- unavailable on this box (no GL/X).
-        Kept as a headless no-op with the same mode check so scripts run unchanged."""
-        assert mode in ['human', 'human_fast']
+        'human' / 'human_fast' stay headless no-ops with the same mode check so scripts run unchanged (render callbacks are
+        not invoked: there is no EnvRenderer to hand them); 'rgb_array' returns the scene rasterised on the GPU as a
+        (WINDOW_H, WINDOW_W, 3) uint8 numpy array, camera on the ego car."""
+        assert mode in ['human', 'human_fast', 'rgb_array']
+        if mode == 'rgb_array':
+            return self.sim._batch.render(mode='rgb_array', envs=1)[0].cpu().numpy()

@@ -227,6 +227,32 @@ int f110_pursuit_plan(f110_pursuit *pp, const double *x_dev, const double *y_dev
                       int64_t stride, double lookahead, double vgain, const double *lookahead_dev, const double *vgain_dev,
                       double *actions_dev, int32_t *picked_dev, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Headless renderer.  F110Env.render (f110_env.py:385-416) draws EnvRenderer's scene
+ * (rendering.py) through pyglet/OpenGL; here the same scene is rasterised into an RGB8 device buffer
+ * (mode 'rgb_array').  No window, no text labels.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct f110_render_config {
+    int32_t abi_version;
+    int32_t width, height;     /* WINDOW_W, WINDOW_H (f110_env.py:50-51) */
+    int32_t n_agents, ego_idx;
+    int32_t map_h, map_w;
+    double resolution, origin_x, origin_y;      /* map yaml (rendering.py:123-129) */
+    double follow_margin;      /* >= 0: camera follows the ego car, bounding box +- margin (examples/waypoint_follow.py:259-269,
+                                  800 there); < 0: the fixed camera below */
+    double left, right, bottom, top;            /* glOrtho bounds in 50 x world units (rendering.py:74-80,290) */
+} f110_render_config;
+
+typedef struct f110_render f110_render;
+
+/* obstacle: host [map_h][map_w] bytes, non-zero where the (top-bottom flipped) map image is exactly 0 (rendering.py:150) */
+int f110_render_create(const f110_render_config *cfg, const uint8_t *obstacle, int device, f110_render **out);
+int f110_render_destroy(f110_render *r);
+/* x_dev / y_dev / theta_dev: DEVICE [n_envs][n_agents] poses (rows 0, 1, 4 of f110_buffers.state);
+ * out_dev: DEVICE [n_envs][height][width][3] bytes, row 0 = top of the window. */
+int f110_render_frame(f110_render *r, const double *x_dev, const double *y_dev, const double *theta_dev, int64_t n_envs,
+                      uint8_t *out_dev, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -24,7 +24,8 @@ EXPORTS = ["f110_last_error", "f110_abi_version", "f110_device_count", "f110_cre
            "f110_reset", "f110_step", "f110_step_host", "f110_raycast", "f110_get_buffers", "f110_get_config",
            "f110_count_lookups", "f110_enable_timing", "f110_last_raycast_ms", "f110_launch_count", "f110_synchronize",
            "f110_bitmap_create", "f110_bitmap_destroy", "f110_bitmap_render",
-           "f110_pursuit_create", "f110_pursuit_destroy", "f110_pursuit_plan"]
+           "f110_pursuit_create", "f110_pursuit_destroy", "f110_pursuit_plan",
+           "f110_render_create", "f110_render_destroy", "f110_render_frame"]
 BITMAP_MODES = {"FILL": 0, "POLYGON": 1, "RAYS": 2}
 
 
@@ -43,6 +44,14 @@ class BitmapConfig(ctypes.Structure):
                 ("height", ctypes.c_int32), ("width", ctypes.c_int32), ("draw_mode", ctypes.c_int32),
                 ("draw_center", ctypes.c_int32), ("bg_white", ctypes.c_int32), ("scan_is_f32", ctypes.c_int32),
                 ("scaling_factor", ctypes.c_double)]
+
+
+class RenderConfig(ctypes.Structure):
+    _fields_ = [("abi_version", ctypes.c_int32), ("width", ctypes.c_int32), ("height", ctypes.c_int32), ("n_agents", ctypes.c_int32),
+                ("ego_idx", ctypes.c_int32), ("map_h", ctypes.c_int32), ("map_w", ctypes.c_int32),
+                ("resolution", ctypes.c_double), ("origin_x", ctypes.c_double), ("origin_y", ctypes.c_double),
+                ("follow_margin", ctypes.c_double), ("left", ctypes.c_double), ("right", ctypes.c_double),
+                ("bottom", ctypes.c_double), ("top", ctypes.c_double)]
 
 
 class Buffers(ctypes.Structure):
@@ -96,6 +105,9 @@ def load():
     L.f110_pursuit_create.argtypes = [vp, vp, vp, i32, f64, f64, ctypes.c_int, ctypes.POINTER(vp)]
     L.f110_pursuit_destroy.argtypes = [vp]
     L.f110_pursuit_plan.argtypes = [vp, vp, vp, vp, i64, i64, f64, f64, vp, vp, vp, vp, vp]
+    L.f110_render_create.argtypes = [ctypes.POINTER(RenderConfig), vp, ctypes.c_int, ctypes.POINTER(vp)]
+    L.f110_render_destroy.argtypes = [vp]
+    L.f110_render_frame.argtypes = [vp, vp, vp, vp, i64, vp, vp]
     for name in EXPORTS:
         fn = getattr(L, name)
         if name not in ("f110_last_error", "f110_launch_count"):

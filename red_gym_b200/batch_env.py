@@ -220,9 +220,39 @@ class BatchF110Env(object):
         self._ensure_noise(self._steps_since_full_reset + 1)
         nat.check(self.lib.f110_step_host(self._h, ptr(actions), ptr(obs_block_out), ptr(scans_out), ptr(done_out), self._stream()))
 
-    def render(self, mode="human"):
-        """The reference renders through pyglet/OpenGL (f110_env.py:385-416): unavailable on this box."""
-        assert mode in ["human", "human_fast"]
+    def render(self, mode="human", envs=None, width=1000, height=800, follow=True, camera=None):
+        """F110Env.render (f110_env.py:385-416).  The reference's window modes 'human' / 'human_fast' need pyglet/OpenGL,
+        which is unavailable on this box: they stay accepted no-ops.  mode='rgb_array' rasterises the same scene
+        (rendering.py: map points, car quads, colours, orthographic camera) on the device and returns a
+        (n, height, width, 3) uint8 CUDA tensor for the first `envs` environments (default: all).
+        follow=True: camera on the ego car like examples/waypoint_follow.py:259-269; else `camera` =
+        (left, right, bottom, top) in 50 x world units, default the reference's start-up window (zoom 1.2)."""
+        assert mode in ["human", "human_fast", "rgb_array"]
+        if mode != "rgb_array":
+            return None
+        torch = self._torch
+        black = getattr(self.map, "black", None)
+        if black is None:
+            raise ValueError("render needs a map loaded from an image (map pixels == 0 are drawn)")
+        if camera is None:
+            camera = (-1.2 * width / 2, 1.2 * width / 2, -1.2 * height / 2, 1.2 * height / 2)
+        key = (id(self.map), int(width), int(height), bool(follow), tuple(float(c) for c in camera))
+        if getattr(self, "_render_key", None) != key:
+            if getattr(self, "_render_h", None):
+                self.lib.f110_render_destroy(self._render_h)
+            cfg = nat.RenderConfig(abi_version=nat.F110_ABI_VERSION, width=int(width), height=int(height), n_agents=self.num_agents,
+                                   ego_idx=self.ego_idx, map_h=self.map.height, map_w=self.map.width, resolution=self.map.resolution,
+                                   origin_x=self.map.origin[0], origin_y=self.map.origin[1], follow_margin=800.0 if follow else -1.0,
+                                   left=camera[0], right=camera[1], bottom=camera[2], top=camera[3])
+            h = ctypes.c_void_p()
+            nat.check(self.lib.f110_render_create(ctypes.byref(cfg), _hp(black), self.device_index, ctypes.byref(h)))
+            self._render_h, self._render_key = h, key
+        n = self.num_envs if envs is None else int(envs)
+        out = torch.empty((n, int(height), int(width), 3), dtype=torch.uint8, device=self.device)
+        s = self.state
+        nat.check(self.lib.f110_render_frame(self._render_h, ctypes.c_void_p(s[0].data_ptr()), ctypes.c_void_p(s[1].data_ptr()),
+                                             ctypes.c_void_p(s[4].data_ptr()), n, ctypes.c_void_p(out.data_ptr()), self._stream()))
+        return out
 
     # ------------------------------------------------------------------ extras
     def raycast(self, poses, out=None):
@@ -261,6 +291,10 @@ class BatchF110Env(object):
         self._torch.cuda.synchronize(self.device)
 
     def close(self):
+        rh = getattr(self, "_render_h", None)
+        if rh:
+            self.lib.f110_render_destroy(rh)
+            self._render_h = None
         h = getattr(self, "_h", None)
         if h:
             self.lib.f110_destroy(h)

@@ -21,6 +21,7 @@ UNITS = [
     ("f110_bitmap.cu", ["-fmad=false"]),
     ("f110_pursuit.cu", ["-fmad=false"]),
     ("f110_edt.cu", ["-fmad=false"]),
+    ("f110_render.cu", ["-fmad=false"]),
     ("f110_abi.cu", []),
 ]
 
@@ -34,7 +35,7 @@ def nvcc():
 
 def sources():
     out = [os.path.join(CSRC, u) for u, _ in UNITS]
-    out += [os.path.join(CSRC, "f110_dev.h"), os.path.join(CSRC, "f110_bitmap_dev.h"), os.path.join(CSRC, "f110_pursuit_dev.h"), os.path.join(os.path.dirname(HERE), "include", "f110_b200.h")]
+    out += [os.path.join(CSRC, "f110_dev.h"), os.path.join(CSRC, "f110_bitmap_dev.h"), os.path.join(CSRC, "f110_pursuit_dev.h"), os.path.join(CSRC, "f110_render_dev.h"), os.path.join(os.path.dirname(HERE), "include", "f110_b200.h")]
     return out
 
 

@@ -11,6 +11,7 @@
 #include "f110_dev.h"
 #include "f110_bitmap_dev.h"
 #include "f110_pursuit_dev.h"
+#include "f110_render_dev.h"
 
 static thread_local std::string g_err;
 static int fail(int code, const char *fmt, ...)
@@ -806,6 +807,66 @@ extern "C" int f110_pursuit_plan(f110_pursuit *p, const double *x_dev, const dou
     CK(cudaSetDevice(p->device));
     f110_launch_pursuit(p->d, x_dev, y_dev, theta_dev, n, stride, lookahead, vgain, lookahead_dev, vgain_dev, actions_dev,
                         (int *)picked_dev, (cudaStream_t)stream);
+    CK(cudaGetLastError());
+    return F110_OK;
+}
+
+// ---- headless renderer (f110_render.cu) ---------------------------------------------------------------------------
+struct f110_render {
+    int device;
+    F110RenderDev d;
+    uint8_t *obstacle = nullptr;
+};
+
+extern "C" int f110_render_create(const f110_render_config *cfg, const uint8_t *obstacle, int device, f110_render **out)
+{
+    if (!cfg || !obstacle || !out) return fail(F110_ERR_INVALID, "null argument");
+    if (cfg->abi_version != F110_ABI_VERSION) return fail(F110_ERR_INVALID, "abi_version %d != %d", cfg->abi_version, F110_ABI_VERSION);
+    if (cfg->width < 1 || cfg->height < 1 || cfg->map_h < 1 || cfg->map_w < 1 || !(cfg->resolution > 0))
+        return fail(F110_ERR_INVALID, "bad renderer sizes");
+    if (cfg->n_agents < 1 || cfg->n_agents > 16 || cfg->ego_idx < 0 || cfg->ego_idx >= cfg->n_agents)
+        return fail(F110_ERR_INVALID, "bad agent count / ego index");
+    if (cfg->follow_margin < 0 && !(cfg->right > cfg->left && cfg->top > cfg->bottom)) return fail(F110_ERR_INVALID, "empty camera window");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(F110_ERR_CUDA, "no CUDA device available; this library has no CPU path");
+    }
+    if (device < 0 || device >= ndev) return fail(F110_ERR_INVALID, "device %d out of range (%d devices)", device, ndev);
+    CK(cudaSetDevice(device));
+    f110_render *r = new f110_render();
+    r->device = device;
+    const size_t cells = (size_t)cfg->map_h * cfg->map_w;
+    if (cudaMalloc(&r->obstacle, cells) != cudaSuccess) { delete r; return fail(F110_ERR_NOMEM, "cudaMalloc failed"); }
+    cudaError_t e = cudaMemcpy(r->obstacle, obstacle, cells, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { cudaFree(r->obstacle); delete r; return fail(F110_ERR_CUDA, "map upload failed: %s", cudaGetErrorString(e)); }
+    F110RenderDev &d = r->d;
+    d.width = cfg->width; d.height = cfg->height; d.n_agents = cfg->n_agents; d.ego_idx = cfg->ego_idx;
+    d.map_h = cfg->map_h; d.map_w = cfg->map_w; d.res = cfg->resolution; d.ox = cfg->origin_x; d.oy = cfg->origin_y;
+    d.obstacle = r->obstacle; d.follow_margin = cfg->follow_margin;
+    d.left = cfg->left; d.right = cfg->right; d.bottom = cfg->bottom; d.top = cfg->top;
+    *out = r;
+    return F110_OK;
+}
+
+extern "C" int f110_render_destroy(f110_render *r)
+{
+    if (!r) return F110_OK;
+    cudaSetDevice(r->device);
+    cudaDeviceSynchronize();
+    if (r->obstacle) cudaFree(r->obstacle);
+    delete r;
+    return F110_OK;
+}
+
+extern "C" int f110_render_frame(f110_render *r, const double *x_dev, const double *y_dev, const double *theta_dev, int64_t n_envs,
+                                 uint8_t *out_dev, void *stream)
+{
+    if (!r) return fail(F110_ERR_INVALID, "null handle");
+    if (n_envs == 0) return F110_OK;
+    if (!x_dev || !y_dev || !theta_dev || !out_dev || n_envs < 0) return fail(F110_ERR_INVALID, "bad render arguments");
+    CK(cudaSetDevice(r->device));
+    f110_launch_render(r->d, x_dev, y_dev, theta_dev, n_envs, out_dev, (cudaStream_t)stream);
     CK(cudaGetLastError());
     return F110_OK;
 }

@@ -41,6 +41,7 @@ class MapData(object):
         occ = np.asarray(Image.open(img_path).transpose(Image.FLIP_TOP_BOTTOM), dtype=np.float64)
         free = occ > 128.0                                   # <=128 -> obstacle, >128 -> free (:403-404)
         self.free = np.ascontiguousarray(free, dtype=np.uint8)
+        self.black = np.ascontiguousarray(occ == 0.0, dtype=np.uint8)     # the pixels EnvRenderer.update_map draws (rendering.py:150)
         with open(map_path, "r") as stream:
             meta = yaml.safe_load(stream)
         self.resolution = float(meta["resolution"])
