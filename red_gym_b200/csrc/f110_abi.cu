@@ -275,6 +275,7 @@ static int set_map_impl(f110_sim *s, const double *edt, const uint8_t *free_px, 
     int ex;
     d.res_pow2 = (frexp(res, &ex) == 0.5);
     d.has_rot = !(oc == 1.0 && os == 0.0);
+    d.magic64 = 4503599627370496.0 * res;
     d.max_c32 = (float)(s->cfg.max_range / res); d.res32 = (float)res;
     d.oob64 = last_cell;                  // dt[-1, -1]
     // fp32 encoding: free cells min(dist, cap), obstacle cells `sent`, max_range < cap < sent (all in cells)

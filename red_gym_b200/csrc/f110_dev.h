@@ -20,6 +20,7 @@ struct F110Dev {
     int map_h, map_w, res_pow2, has_rot;
     double res, inv_res, ox, oy, oc, os, xmax, ymax;
     double oob64;                      // dt[-1,-1] : value an out-of-map lookup returns
+    double magic64;                    // res_pow2: 2^52 * res, so that v + magic64 (round toward zero) holds floor(v / res) in its low word
     float oob32;
     const double *edt64;               // row-major [h][w], metres
     const float *edt32;                // row-major [h][w], in CELL units (metres / res); obstacle cells hold sent32 (see fp32 kernels)

@@ -119,6 +119,35 @@ def test_config4_two_agents_vs_oracle():
     assert (ora.collision_idx >= 0).any()      # GJK did fire
 
 
+def test_opponent_raycast_random_placements():
+    """ray_cast_agents with three cars per env placed anywhere around each other (in front, beside, behind -- where the
+    reference casts the whole scan --, overlapping): scans right after reset against the oracle.  A beam grazing a corner
+    may fall on the other side in the last ulp of sin/cos, hence the (tiny) allowance."""
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    N, A = 4096, 3
+    rng = np.random.default_rng(44)
+    poses = np.repeat(raceline_poses(N)[:, None, :], A, axis=1)
+    poses[:, 1:, 0] += rng.uniform(-3.0, 3.0, (N, A - 1))
+    poses[:, 1:, 1] += rng.uniform(-3.0, 3.0, (N, A - 1))
+    poses[:, 1:, 2] = rng.uniform(-np.pi, np.pi, (N, A - 1))
+    poses[: N // 8, 1, :2] = poses[: N // 8, 0, :2] + rng.uniform(-0.3, 0.3, (N // 8, 2))     # overlapping cars
+    kw = dict(map=os.path.join(MAPS, "example_map"), seed=5)
+    env = BatchF110Env(num_envs=N, num_agents=A, **kw)
+    ora = fo.OracleEnv(N, A, noise_rows=8, **kw)
+    env.reset(poses)
+    ora.reset(poses)
+    got, want = env.scans.cpu().numpy(), ora.scans
+    assert (env.collisions.cpu().numpy() == ora.collisions).all()
+    assert (env.collision_idx.cpu().numpy() == ora.collision_idx).all()
+    assert (ora.collision_idx >= 0).sum() >= N // 8
+    off = np.abs(got - want) > 1e-9
+    assert off.mean() < 1e-6, (off.sum(), np.abs(got - want).max())
+    # the opponents do show in the scans: the same poses one car at a time give longer ranges somewhere in most envs
+    solo = ora.scan(poses.reshape(-1, 3)).reshape(N, A, -1)
+    assert ((solo - want) > 0.05).any(axis=2).mean() > 0.5
+
+
 def test_masked_reset_and_param_update():
     from red_gym_b200 import BatchF110Env
     from red_gym_b200.host import raceline_poses, DEFAULT_PARAMS
