@@ -240,11 +240,24 @@ static __device__ __forceinline__ double theta_start(const F110Dev &d, double ya
     return t;
 }
 
+// Per-scan data, one row per warp in shared memory (at 40 registers a thread has no room for them, and ptxas
+// would otherwise recompute them beam after beam).  x_lo .. y_hi hoist the bounds test out of the loop: distances
+// (metres, map frame) from the scan origin to the map border minus a 2-cell margin.  While the accumulated range of
+// a ray is below the range at which it crosses that margin, every lookup is inside the map and the test of
+// xy_2_rc (:79) is provably false -- skipping it changes no result.
+struct __align__(16) Scan64 {
+    float x_lo, x_hi, y_lo, y_hi;
+    double px, py, d0, t0, vel, r_gate;
+    double *out;
+    const double *noise;
+    float max_fast, pad_;
+};
+
 // Table index of beam i.  The reference accumulates theta_index += increment beam after beam
 // (laser_models.py:180-184) and truncates; the closed form t0 + i*inc differs from that running
 // sum by < 2160 * 2^-43 < 3e-10, so int() can only differ within 1e-9 of an integer -- those beams
 // replay the sequential sum exactly.
-static __device__ __forceinline__ int theta_index_of(const F110Dev &d, double t0, int i, double a)
+static __device__ __forceinline__ int theta_index_of(const F110Dev &d, const Scan64 *c, int i, double a)
 {
     // a ~ t0 + i*inc (closed form, accumulated per round: a few 1e-12 off at most)
     double td = (double)d.theta_dis;
@@ -253,7 +266,7 @@ static __device__ __forceinline__ int theta_index_of(const F110Dev &d, double t0
     unsigned lo = (unsigned)__double2loint(tz), hi = (unsigned)__double2hiint(tz);
     int k = (int)(__funnelshift_l(lo, hi, 2) & 0x3FFFFFu);
     if (((lo + 2u) & 0x3FFFFFFFu) < 4u) {
-        double t = t0;
+        double t = c->t0;
         for (int j = 0; j < i; j++) {
             t += d.theta_inc;
             while (t >= td) t -= td;
@@ -264,40 +277,41 @@ static __device__ __forceinline__ int theta_index_of(const F110Dev &d, double t0
     return k;
 }
 
-// Per-scan data for hoisting the bounds test out of the loop: distances (metres, map frame) from the
-// scan origin to the map border minus a 2-cell margin.  While the accumulated range of a ray is below
-// the range at which it crosses that margin, every lookup is inside the map and the test of
-// xy_2_rc (:79) is provably false -- skipping it changes no result.
-struct Scan64 {
-    double px, py, d0, t0;
-    float x_lo, x_hi, y_lo, y_hi, max_fast;
-};
-
-template <bool ROT>
-static __device__ __forceinline__ void scan_setup64(const F110Dev &d, double px, double py, double yaw, Scan64 &c)
+template <bool ROT, bool POW2, bool STEP>
+static __device__ __forceinline__ void scan_setup64(const F110Dev &d, double px, double py, double yaw, double vel,
+                                                    double *out, const double *noise_row, Scan64 *c)
 {
-    c.px = px; c.py = py;
-    c.t0 = theta_start(d, yaw);
     double xt = px - d.ox, yt = py - d.oy;
     double xr = ROT ? xt * d.oc + yt * d.os : xt;
     double yr = ROT ? -xt * d.os + yt * d.oc : yt;
     float margin = 2.0f * (float)d.res;
-    c.x_lo = margin - (float)xr; c.x_hi = (float)d.xmax - margin - (float)xr;
-    c.y_lo = margin - (float)yr; c.y_hi = (float)d.ymax - margin - (float)yr;
-    c.max_fast = (c.x_lo <= 0.f && c.x_hi >= 0.f && c.y_lo <= 0.f && c.y_hi >= 0.f) ? (float)d.max_range : -1.0f;
+    float x_lo = margin - (float)xr, x_hi = (float)d.xmax - margin - (float)xr;
+    float y_lo = margin - (float)yr, y_hi = (float)d.ymax - margin - (float)yr;
+    double d0 = edt_lookup<ROT, POW2, true>(d, px, py);
+    double t0 = theta_start(d, yaw);
+    if ((threadIdx.x & 31) == 0) {
+        c->x_lo = x_lo; c->x_hi = x_hi; c->y_lo = y_lo; c->y_hi = y_hi;
+        c->max_fast = (x_lo <= 0.f && x_hi >= 0.f && y_lo <= 0.f && y_hi >= 0.f) ? (float)d.max_range : -1.0f;
+        c->px = px; c->py = py; c->d0 = d0; c->t0 = t0; c->vel = vel;
+        // iTTC (laser_models.py:208-213) needs 0 <= (r - side)/(v cos) < thresh, impossible for r >= side_max + 1.2*thresh*|v|
+        c->r_gate = (STEP && vel != 0.0) ? (double)d.side_max32 * 1.0001 + 1.2 * d.ttc_thresh * fabs(vel) : -1.0;
+        c->out = out; c->noise = noise_row;
+    }
+    __syncwarp();
 }
 
 // trace_ray (laser_models.py:107-146) given the first lookup d0 at the scan origin
 template <bool ROT, bool POW2, bool COUNT>
-static __device__ __forceinline__ double trace_ray(const F110Dev &d, const Scan64 &c, int ti, unsigned &nlook)
+static __device__ __forceinline__ double trace_ray(const F110Dev &d, const Scan64 *c, int ti, unsigned &nlook)
 {
     const double sn = __ldg(d.sines + ti), cs = __ldg(d.cosines + ti);
     // fp32 estimate (conservative through the margin) of the range where the ray nears the border
     const float4 dir = __ldg(d.dir32 + ti);
-    float tx = (dir.x > 0.f ? c.x_hi : c.x_lo) * dir.z;
-    float ty = (dir.y > 0.f ? c.y_hi : c.y_lo) * dir.w;
-    const double t_fast = (double)fminf(fminf(tx, ty), c.max_fast);
-    double x = c.px, y = c.py, dist = c.d0, total = c.d0;
+    const float4 lim = *reinterpret_cast<const float4 *>(c);
+    float tx = (dir.x > 0.f ? lim.y : lim.x) * dir.z;
+    float ty = (dir.y > 0.f ? lim.w : lim.z) * dir.w;
+    const double t_fast = (double)fminf(fminf(tx, ty), c->max_fast);
+    double x = c->px, y = c->py, dist = c->d0, total = dist;
     // The two tests of the fast loop compare high words with integer instructions (off the FP64 pipe): both are
     // one-sided -- hi(dist) > hi(eps) implies dist > eps, hi(total) < hi(t_fast) implies total < t_fast (negative
     // values have a negative high word) -- and whatever they leave undecided the exact loop below decides.
@@ -335,37 +349,26 @@ static __device__ __forceinline__ bool ttc_hit(double range, double side, double
 // cells, so a warp-level gather touches few cache lines); lanes whose ray has converged idle until
 // the round's slowest ray is done.
 template <bool ROT, bool POW2, bool STEP, bool COUNT>
-static __device__ __forceinline__ void scan_rounds(const F110Dev &d, double px, double py, double yaw,
-                                                   double *__restrict__ out, const double *__restrict__ noise_row,
-                                                   double vel, bool &hit_any, unsigned &nlook)
+static __device__ __forceinline__ void scan_rounds(const F110Dev &d, const Scan64 *c, bool &hit_any, unsigned &nlook)
 {
     const int lane = threadIdx.x & 31;
-    Scan64 c;
-    scan_setup64<ROT>(d, px, py, yaw, c);
-    c.d0 = edt_lookup<ROT, POW2, true>(d, px, py);
     if (COUNT) nlook += (lane == 0);
-    // running per-lane values: output / noise pointers and the closed-form beam index t0 + i*inc
-    double *op = out + lane;
-    const double *np_ = noise_row ? noise_row + lane : nullptr;
-    double a = c.t0 + (double)lane * d.theta_inc;
-    const double a_step = 32.0 * d.theta_inc;
-    // iTTC (laser_models.py:208-213) needs 0 <= (r - side)/(v cos) < thresh, impossible for r >= side_max + 1.2*thresh*|v|
-    const double r_gate = (STEP && vel != 0.0) ? (double)d.side_max32 * 1.0001 + 1.2 * d.ttc_thresh * fabs(vel) : -1.0;
-    for (int base = 0; base < d.n_beams; base += 32) {
-        int i = base + lane;
-        if (i < d.n_beams) {
-            int ti = theta_index_of(d, c.t0, i, a);
-            double r = trace_ray<ROT, POW2, COUNT>(d, c, ti, nlook);
-            if (np_) r += __ldg(np_ + base);
-            op[base] = r;
-            if (r < r_gate)
-                hit_any |= ttc_hit(r, __ldg(d.side_dist + i), vel, __ldg(d.beam_cos + i), d.ttc_thresh);
-        }
-        a += a_step;
+    // closed-form beam index t0 + i*inc, carried per lane
+    double a = c->t0 + (double)lane * d.theta_inc;
+    for (int i = lane; i < d.n_beams; i += 32) {
+        int ti = theta_index_of(d, c, i, a);
+        double r = trace_ray<ROT, POW2, COUNT>(d, c, ti, nlook);
+        const double *np_ = c->noise;
+        if (np_) r += __ldg(np_ + i);
+        c->out[i] = r;
+        if (STEP && r < c->r_gate)
+            hit_any |= ttc_hit(r, __ldg(d.side_dist + i), c->vel, __ldg(d.beam_cos + i), d.ttc_thresh);
+        a += 32.0 * d.theta_inc;
     }
 }
 
-// MINB = 6 (40 registers, 48 warps per SM) measured best: 64 regs 4.34 ms, 48 regs 4.08 ms, 40 regs 3.92 ms per 262144 scans
+// per 262144 scans (example_map, power-of-two resolution): 64 regs 4.34 ms, 48 regs 4.08 ms, 40 regs 3.92 ms with the per-scan
+// constants in registers; with the shared-memory row 40 regs 3.37 ms, 32 regs (MINB = 8, no spill) 3.09 ms
 template <bool ROT, bool POW2, bool COUNT, int MINB>
 __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int env_begin, int env_count)
 {
@@ -387,7 +390,10 @@ __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int en
     }
     bool hit = false;
     unsigned nlook = 0;
-    scan_rounds<ROT, POW2, true, COUNT>(d, px, py, yaw, (double *)d.scans + (size_t)ia * d.n_beams, noise_row, vel, hit, nlook);
+    __shared__ Scan64 rows[8];
+    Scan64 *c = rows + (threadIdx.x >> 5);
+    scan_setup64<ROT, POW2, true>(d, px, py, yaw, vel, (double *)d.scans + (size_t)ia * d.n_beams, noise_row, c);
+    scan_rounds<ROT, POW2, true, COUNT>(d, c, hit, nlook);
     hit = __any_sync(FULL, hit);
     // RaceCar.check_ttc (base_classes.py:241-250): state[3:] = 0 -- velocity, YAW, yaw rate, slip
     if (lane == 0) {
@@ -413,8 +419,10 @@ __global__ void __launch_bounds__(256) k_scan_only64(const F110Dev d, const doub
     if (order) w = order[w];
     bool hit = false;
     unsigned nlook = 0;
-    scan_rounds<ROT, POW2, false, COUNT>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], out + (size_t)w * d.n_beams,
-                                         nullptr, 0.0, hit, nlook);
+    __shared__ Scan64 rows[8];
+    Scan64 *c = rows + (threadIdx.x >> 5);
+    scan_setup64<ROT, POW2, false>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], 0.0, out + (size_t)w * d.n_beams, nullptr, c);
+    scan_rounds<ROT, POW2, false, COUNT>(d, c, hit, nlook);
     if (COUNT) {
 #pragma unroll
         for (int o = 16; o; o >>= 1) nlook += __shfl_xor_sync(FULL, nlook, o);
@@ -443,15 +451,16 @@ void f110_launch_raycast64(const F110Dev &d, int env_begin, int env_count, int v
     int grid = (int)((warps * 32 + 255) / 256);
     if (grid == 0) return;
     const bool cnt = d.count_lookups != 0;
-#define RC64(R, P)                                                                                       \
+#define RC64(R, P, MB, ALT)                                                                                \
     do {                                                                                                 \
         if (cnt) k_raycast64<R, P, true, 1><<<grid, 256, 0, st>>>(d, env_begin, env_count);              \
-        else if (variant & 8) k_raycast64<R, P, false, 8><<<grid, 256, 0, st>>>(d, env_begin, env_count); \
-        else k_raycast64<R, P, false, 6><<<grid, 256, 0, st>>>(d, env_begin, env_count);                 \
+        else if (variant & 8) k_raycast64<R, P, false, ALT><<<grid, 256, 0, st>>>(d, env_begin, env_count); \
+        else k_raycast64<R, P, false, MB><<<grid, 256, 0, st>>>(d, env_begin, env_count);                \
     } while (0)
-    if (d.has_rot) RC64(true, false);
-    else if (d.res_pow2) RC64(false, true);
-    else RC64(false, false);
+    // registers per thread: 32 (8 CTAs per SM) where the kernel fits without spilling, else 40; variant bit 3 swaps the two
+    if (d.has_rot) RC64(true, false, 6, 8);
+    else if (d.res_pow2) RC64(false, true, 8, 6);
+    else RC64(false, false, 6, 8);
 #undef RC64
 }
 
