@@ -400,6 +400,10 @@ def run_downstream(args):
     act = torch.empty((n, 1, 2), dtype=torch.float64, device=device)
     ms = timeit(lambda: pl.plan_actions(env, 0.82461887897713965, 1.375, out=act))
     res["pure_pursuit"] = {"ms": ms, "plans_per_s": n / (ms * 1e-3), "segments_per_plan": 782}
+    # the same poses 16 times over in one launch: at 65 536 cars the call is shorter than its own host-side overhead
+    big = [env.state[k].reshape(-1).repeat(16).contiguous() for k in (0, 1, 4)]
+    ms = timeit(lambda: pl.plan(big[0], big[1], big[2], 0.82461887897713965, 1.375))
+    res["pure_pursuit_16x"] = {"ms": ms, "plans": 16 * n, "plans_per_s": 16 * n / (ms * 1e-3)}
     cpu = None
     if not args.no_cpu:
         sys.path.insert(0, os.path.join(REPO, "oracle"))

@@ -766,7 +766,7 @@ extern "C" int f110_pursuit_create(const double *wx, const double *wy, const dou
 {
     if (!wx || !wy || !wv || !out) return fail(F110_ERR_INVALID, "null argument");
     if (n < 2 || n > 65536) return fail(F110_ERR_INVALID, "need 2 <= n_waypoints <= 65536");
-    if ((size_t)3 * n * 8 > 200 * 1024) return fail(F110_ERR_INVALID, "raceline too long for the shared-memory planner (%d waypoints)", n);
+    if (((size_t)6 * n + 3 * (size_t)(n / 16 + 1)) * 8 > 200 * 1024) return fail(F110_ERR_INVALID, "raceline too long for the shared-memory planner (%d waypoints)", n);
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) {

@@ -7,8 +7,15 @@
 //   look-ahead target is the START waypoint of the intersected segment, its speed comes from the NEAREST segment's
 //   waypoint, segment ends are shifted by 1e-6, no target -> (speed 4.0, steer 0.0).
 // fp64, compiled with -fmad=false.  The polyline (x, y, v) sits in shared memory.
+//
+// nearest_point_on_trajectory is an argmin over every segment (782 on example_waypoints); a car is near a handful.
+// Segments are taken in groups of 16 with a bounding circle each; a group whose circle is farther away than a
+// segment distance already known cannot hold the minimum and is skipped, the others are evaluated exactly, in
+// index order (np.argmin returns the FIRST minimum).  Same result, ~50 circle tests + ~50 exact segments per car
+// instead of 782 exact segments with an IEEE division each.
 #include <cuda_runtime.h>
 #include <math.h>
+#include <math_constants.h>
 #include <stdint.h>
 #include "f110_pursuit_dev.h"
 
@@ -29,6 +36,8 @@ static __device__ __forceinline__ bool circle_hit(const double *wx, const double
     return true;
 }
 
+#define PP_GROUP 16
+
 __global__ void __launch_bounds__(128) k_pure_pursuit(const F110PursuitDev d, const double *__restrict__ xs,
                                                       const double *__restrict__ ys, const double *__restrict__ thetas,
                                                       long long n, long long stride, double lookahead, double vgain,
@@ -36,30 +45,71 @@ __global__ void __launch_bounds__(128) k_pure_pursuit(const F110PursuitDev d, co
                                                       double *__restrict__ actions, int *__restrict__ picked)
 {
     extern __shared__ double sm[];
-    const int nw = d.n_waypoints;
+    const int nw = d.n_waypoints, nseg = nw - 1, ng = (nseg + PP_GROUP - 1) / PP_GROUP;
     double *wx = sm, *wy = sm + nw, *wv = sm + 2 * nw;
+    double *sdx = sm + 3 * nw, *sdy = sm + 4 * nw, *sl2 = sm + 5 * nw;       // diffs and l2s of the reference (:27-28)
+    double *gcx = sm + 6 * nw, *gcy = gcx + ng, *gr = gcy + ng;              // bounding circle of each group of segments
     for (int i = threadIdx.x; i < nw; i += blockDim.x) { wx[i] = d.wx[i]; wy[i] = d.wy[i]; wv[i] = d.wv[i]; }
+    __syncthreads();
+    for (int i = threadIdx.x; i < nseg; i += blockDim.x) {
+        const double dx = wx[i + 1] - wx[i], dy = wy[i + 1] - wy[i];
+        sdx[i] = dx; sdy[i] = dy; sl2[i] = dx * dx + dy * dy;
+    }
+    for (int g = threadIdx.x; g < ng; g += blockDim.x) {
+        const int k0 = g * PP_GROUP, k1 = min(k0 + PP_GROUP, nseg);             // way points k0 .. k1 span the group's segments
+        double cx = 0.0, cy = 0.0;
+        for (int k = k0; k <= k1; k++) { cx += wx[k]; cy += wy[k]; }
+        cx /= (double)(k1 - k0 + 1); cy /= (double)(k1 - k0 + 1);
+        double r2 = 0.0;
+        for (int k = k0; k <= k1; k++) r2 = fmax(r2, (wx[k] - cx) * (wx[k] - cx) + (wy[k] - cy) * (wy[k] - cy));
+        gcx[g] = cx; gcy[g] = cy; gr[g] = sqrt(r2) * (1.0 + 1e-9) + 1e-12;      // NaN way points: NaN radius, never skipped
+    }
     __syncthreads();
     const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
     const double px = xs[q * stride], py = ys[q * stride], th = thetas[q * stride];
     const double ld = lookahead_q ? lookahead_q[q] : lookahead;
     const double vg = vgain_q ? vgain_q[q] : vgain;
+    // an upper bound of the minimum: the closest way point of the group whose centre is closest
+    int gs = 0;
+    double gd = CUDART_INF;
+    for (int g = 0; g < ng; g++) {
+        const double ex = px - gcx[g], ey = py - gcy[g];
+        const double c2 = ex * ex + ey * ey;
+        if (c2 < gd) { gd = c2; gs = g; }
+    }
+    double bound2 = CUDART_INF;
+    for (int k = gs * PP_GROUP; k <= min(gs * PP_GROUP + PP_GROUP, nseg); k++) {
+        const double ex = px - wx[k], ey = py - wy[k];
+        bound2 = fmin(bound2, ex * ex + ey * ey);
+    }
+    double reach = sqrt(bound2) * (1.0 + 1e-9) + 1e-12;                          // groups farther than this are out
     // nearest_point_on_trajectory: first minimum of the point-to-segment distances (np.argmin)
     int bi = 0;
+    bool none = true;
     double bd = 0.0, bt = 0.0, bd2 = 0.0;
-    for (int i = 0; i + 1 < nw; i++) {
-        const double dx = wx[i + 1] - wx[i], dy = wy[i + 1] - wy[i];
-        const double l2 = dx * dx + dy * dy;
-        double t = ((px - wx[i]) * dx + (py - wy[i]) * dy) / l2;
-        if (t < 0.0) t = 0.0;
-        if (t > 1.0) t = 1.0;
-        const double ex = px - (wx[i] + t * dx), ey = py - (wy[i] + t * dy);
-        const double d2 = ex * ex + ey * ey;
-        // sqrt only for candidates: d2 >= best d2 cannot give a strictly smaller rounded root
-        if (i == 0 || d2 < bd2 || d2 != d2) {
-            const double dist = sqrt(d2);
-            if (i == 0 || dist < bd || (dist != dist && bd == bd)) { bd = dist; bt = t; bi = i; bd2 = d2; }
+    for (int g = 0; g < ng; g++) {
+        {
+            const double ex = px - gcx[g], ey = py - gcy[g];
+            const double lim = gr[g] + reach;
+            if (ex * ex + ey * ey > lim * lim) continue;                         // false for NaN: evaluated
+        }
+        const int i1 = min(g * PP_GROUP + PP_GROUP, nseg);
+        for (int i = g * PP_GROUP; i < i1; i++) {
+            const double dx = sdx[i], dy = sdy[i];
+            double t = ((px - wx[i]) * dx + (py - wy[i]) * dy) / sl2[i];
+            if (t < 0.0) t = 0.0;
+            if (t > 1.0) t = 1.0;
+            const double ex = px - (wx[i] + t * dx), ey = py - (wy[i] + t * dy);
+            const double d2 = ex * ex + ey * ey;
+            // sqrt only for candidates: d2 >= best d2 cannot give a strictly smaller rounded root
+            if (none || d2 < bd2 || d2 != d2) {
+                const double dist = sqrt(d2);
+                if (none || dist < bd || (dist != dist && bd == bd)) {
+                    bd = dist; bt = t; bi = i; bd2 = d2; none = false;
+                    reach = fmin(reach, dist * (1.0 + 1e-9) + 1e-12);
+                }
+            }
         }
     }
     bool have = false;
@@ -105,7 +155,8 @@ void f110_launch_pursuit(const F110PursuitDev &d, const double *x, const double 
                          double *actions, int *picked, cudaStream_t st)
 {
     if (n <= 0) return;
-    const size_t smem = (size_t)3 * d.n_waypoints * sizeof(double);
+    const int ng = (d.n_waypoints - 1 + PP_GROUP - 1) / PP_GROUP;
+    const size_t smem = ((size_t)6 * d.n_waypoints + 3 * (size_t)(ng > 0 ? ng : 0)) * sizeof(double);
     if (smem > 48 * 1024) cudaFuncSetAttribute(k_pure_pursuit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k_pure_pursuit<<<(unsigned)((n + 127) / 128), 128, smem, st>>>(d, x, y, theta, n, stride, lookahead, vgain, lookahead_q, vgain_q,
                                                                    actions, picked);

@@ -26,6 +26,34 @@ def test_random_poses_match_reference_planner():
     assert np.abs(st.cpu().numpy() - want[:, 1]).max() <= 1e-12         # CUDA sin/cos/atan vs glibc
 
 
+def test_nearest_segment_search_prunes_nothing_it_needs():
+    """The planner skips groups of segments that cannot hold the nearest point: the nearest index (np.argmin, first
+    minimum) must still be the oracle's for cars on the line, between two parts of it, far outside the map, and exactly
+    on way points (ties between the two segments that share one)."""
+    import pursuit_oracle as po
+    from red_gym_b200 import BatchPurePursuitPlanner
+    wp = po.load_waypoints(CONF.wpt_path, CONF.wpt_delim, CONF.wpt_rowskip)
+    xy = wp[:, [CONF.wpt_xind, CONF.wpt_yind]]
+    rng = np.random.default_rng(7)
+    lo, hi = xy.min(axis=0), xy.max(axis=0)
+    pts = [xy[rng.integers(0, len(xy), 1500)] + rng.normal(0, 0.4, (1500, 2)),            # around the line
+           rng.uniform(lo - 5, hi + 5, (1500, 2)),                                          # anywhere over the map
+           rng.uniform(-500, 500, (300, 2)),                                                # far away
+           xy[rng.integers(0, len(xy), 300)],                                               # on way points
+           0.5 * (xy[:-1] + xy[1:])[rng.integers(0, len(xy) - 1, 300)]]                     # on segment mid points
+    pts = np.concatenate(pts)
+    th = rng.uniform(-np.pi, np.pi, len(pts))
+    pl = BatchPurePursuitPlanner(CONF, WB)
+    sp, st, picked = pl.plan(pts[:, 0], pts[:, 1], th, 1.5, 1.0, return_picked=True)
+    picked = picked.cpu().numpy()
+    for k in range(len(pts)):
+        (w_sp, w_st), (i, i2) = po.plan(wp, pts[k, 0], pts[k, 1], th[k], 1.5, 1.0, WB, CONF.wpt_xind, CONF.wpt_yind, CONF.wpt_vind,
+                                        return_index=True)
+        # second index: the intersected segment; the kernel reports the nearest index again when it re-acquires the line
+        assert picked[k, 0] == i and picked[k, 1] in ((i2,) if i2 != -2 else (-2, i)), (k, pts[k], picked[k], i, i2)
+        assert sp[k].item() == w_sp and abs(st[k].item() - w_st) <= 1e-12
+
+
 def test_waypoint_follow_pose_action_pairs():
     from red_gym_b200 import BatchPurePursuitPlanner
     d = np.load(os.path.join(GOLDEN, "waypoint_follow.npz"))
