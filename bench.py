@@ -263,6 +263,20 @@ def run_b200(args):
                "h2d_bytes_per_step": act_h.numel() * 8 * world,
                "d2h_bytes_per_step": (obs_h.numel() * 8 + scans_h.numel() * scans_h.element_size() + done_h.numel()) * world,
                "steps": Ke, "api": "f110_step_host (C ABI, pinned host buffers, full observation incl. scans copied back)"}
+        # informational: the same call with scans_host = NULL (scans stay in HBM for a device-side consumer such as the
+        # bitmap rasteriser / a policy; poses, velocities, flags and done still come back every step)
+        for _ in range(2):
+            env.step_host(act_h, obs_h, None, done_h)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            env.step_host(act_h, obs_h, None, done_h)
+        torch.cuda.synchronize()
+        ts = torch.tensor([time.perf_counter() - t0], device=device, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        e2e["scans_on_device"] = {"value": float(n_envs) * agents * Ke * world / float(ts.item()), "unit": "agent-steps/s",
+                                  "d2h_bytes_per_step": (obs_h.numel() * 8 + done_h.numel()) * world}
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu:
