@@ -8,6 +8,13 @@ enum { F110_P_MU, F110_P_CSF, F110_P_CSR, F110_P_LF, F110_P_LR, F110_P_H, F110_P
        F110_P_SMAX, F110_P_SVMIN, F110_P_SVMAX, F110_P_VSWITCH, F110_P_AMAX, F110_P_VMIN, F110_P_VMAX,
        F110_P_WIDTH, F110_P_LENGTH, F110_NP };
 
+// Launches of fewer scans than this give each scan a CTA of 8 warps instead of one warp (k_*split / SPLIT = true):
+// one warp per scan would leave most of the GPU waiting on ~365 dependent gathers in a row.  Measured per step,
+// split / one warp per scan: fp64 256 envs 0.073 / 0.138 ms, 4096 envs 0.142 / 0.173, 8192 envs 0.221 / 0.196;
+// fp32 256 envs 0.061 / 0.095, 4096 envs 0.127 / 0.123, 8192 envs 0.193 / 0.139.  Variant bit 7 turns it off.
+#define F110_SPLIT_BELOW64 6144
+#define F110_SPLIT_BELOW32 3072
+
 struct F110Dev {
     int n_envs, n_agents, n_beams, integrator, ego_idx, theta_dis;
     int noise_mode, auto_reset, count_lookups, n_pool, scan_is_f32, env_offset;

@@ -348,14 +348,18 @@ static __device__ __forceinline__ bool ttc_hit(double range, double side, double
 // One warp per scan, 32 consecutive beams in lockstep per round (adjacent beams hit adjacent EDT
 // cells, so a warp-level gather touches few cache lines); lanes whose ray has converged idle until
 // the round's slowest ray is done.
+// A scan may also be split over the `stride` warps of a CTA (warp r0 takes rounds r0, r0 + stride, ...): below
+// ~32 768 scans one warp per scan leaves the GPU waiting on 365 dependent gathers in a row per warp.
 template <bool ROT, bool POW2, bool STEP, bool COUNT>
-static __device__ __forceinline__ void scan_rounds(const F110Dev &d, const Scan64 *c, bool &hit_any, unsigned &nlook)
+static __device__ __forceinline__ void scan_rounds(const F110Dev &d, const Scan64 *c, bool &hit_any, unsigned &nlook,
+                                                   int r0 = 0, int stride = 1)
 {
     const int lane = threadIdx.x & 31;
-    if (COUNT) nlook += (lane == 0);
+    if (COUNT) nlook += (lane == 0 && r0 == 0);
     // closed-form beam index t0 + i*inc, carried per lane
-    double a = c->t0 + (double)lane * d.theta_inc;
-    for (int i = lane; i < d.n_beams; i += 32) {
+    double a = c->t0 + (double)(lane + 32 * r0) * d.theta_inc;
+    const double a_step = (double)(32 * stride) * d.theta_inc;
+    for (int i = lane + 32 * r0; i < d.n_beams; i += 32 * stride) {
         int ti = theta_index_of(d, c, i, a);
         double r = trace_ray<ROT, POW2, COUNT>(d, c, ti, nlook);
         const double *np_ = c->noise;
@@ -363,17 +367,18 @@ static __device__ __forceinline__ void scan_rounds(const F110Dev &d, const Scan6
         c->out[i] = r;
         if (STEP && r < c->r_gate)
             hit_any |= ttc_hit(r, __ldg(d.side_dist + i), c->vel, __ldg(d.beam_cos + i), d.ttc_thresh);
-        a += 32.0 * d.theta_inc;
+        a += a_step;
     }
 }
 
 // per 262144 scans (example_map, power-of-two resolution): 64 regs 4.34 ms, 48 regs 4.08 ms, 40 regs 3.92 ms with the per-scan
 // constants in registers; with the shared-memory row 40 regs 3.37 ms, 32 regs (MINB = 8, no spill) 3.09 ms
-template <bool ROT, bool POW2, bool COUNT, int MINB>
+// SPLIT: one CTA (8 warps) per scan instead of one warp per scan
+template <bool ROT, bool POW2, bool COUNT, int MINB, bool SPLIT>
 __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int env_begin, int env_count)
 {
     const int NA = d.n_envs * d.n_agents;
-    int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int w = SPLIT ? (int)blockIdx.x : (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (w >= env_count * d.n_agents) return;
     int ia = env_begin * d.n_agents + w;
     if (d.order) ia = d.order[ia];      // spatial launch order (f110_order.cu)
@@ -391,12 +396,19 @@ __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int en
     bool hit = false;
     unsigned nlook = 0;
     __shared__ Scan64 rows[8];
-    Scan64 *c = rows + (threadIdx.x >> 5);
-    scan_setup64<ROT, POW2, true>(d, px, py, yaw, vel, (double *)d.scans + (size_t)ia * d.n_beams, noise_row, c);
-    scan_rounds<ROT, POW2, true, COUNT>(d, c, hit, nlook);
-    hit = __any_sync(FULL, hit);
+    Scan64 *c = rows + (SPLIT ? 0 : (threadIdx.x >> 5));
+    if (!SPLIT || threadIdx.x < 32)
+        scan_setup64<ROT, POW2, true>(d, px, py, yaw, vel, (double *)d.scans + (size_t)ia * d.n_beams, noise_row, c);
+    if (SPLIT) {
+        __syncthreads();                        // one row for the CTA, written by its first warp
+        scan_rounds<ROT, POW2, true, COUNT>(d, c, hit, nlook, threadIdx.x >> 5, 8);
+        hit = __syncthreads_or(hit) != 0;       // every warp has read the state by now (the returns above are per CTA)
+    } else {
+        scan_rounds<ROT, POW2, true, COUNT>(d, c, hit, nlook);
+        hit = __any_sync(FULL, hit);
+    }
     // RaceCar.check_ttc (base_classes.py:241-250): state[3:] = 0 -- velocity, YAW, yaw rate, slip
-    if (lane == 0) {
+    if (lane == 0 && (!SPLIT || threadIdx.x == 0)) {
         if (hit) {
             d.state[3 * (size_t)NA + ia] = 0.; d.state[4 * (size_t)NA + ia] = 0.;
             d.state[5 * (size_t)NA + ia] = 0.; d.state[6 * (size_t)NA + ia] = 0.;
@@ -410,19 +422,22 @@ __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int en
     }
 }
 
-template <bool ROT, bool POW2, bool COUNT>
+template <bool ROT, bool POW2, bool COUNT, bool SPLIT>
 __global__ void __launch_bounds__(256) k_scan_only64(const F110Dev d, const double *__restrict__ poses, int n,
                                                      double *__restrict__ out, const int *__restrict__ order)
 {
-    int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int w = SPLIT ? (int)blockIdx.x : (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (w >= n) return;
     if (order) w = order[w];
     bool hit = false;
     unsigned nlook = 0;
     __shared__ Scan64 rows[8];
-    Scan64 *c = rows + (threadIdx.x >> 5);
-    scan_setup64<ROT, POW2, false>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], 0.0, out + (size_t)w * d.n_beams, nullptr, c);
-    scan_rounds<ROT, POW2, false, COUNT>(d, c, hit, nlook);
+    Scan64 *c = rows + (SPLIT ? 0 : (threadIdx.x >> 5));
+    if (!SPLIT || threadIdx.x < 32)
+        scan_setup64<ROT, POW2, false>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], 0.0, out + (size_t)w * d.n_beams, nullptr, c);
+    if (SPLIT) __syncthreads();
+    if (SPLIT) scan_rounds<ROT, POW2, false, COUNT>(d, c, hit, nlook, threadIdx.x >> 5, 8);
+    else scan_rounds<ROT, POW2, false, COUNT>(d, c, hit, nlook);
     if (COUNT) {
 #pragma unroll
         for (int o = 16; o; o >>= 1) nlook += __shfl_xor_sync(FULL, nlook, o);
@@ -430,32 +445,37 @@ __global__ void __launch_bounds__(256) k_scan_only64(const F110Dev d, const doub
     }
 }
 
-#define DISPATCH64(KERNEL, GRID, ...)                                                             \
+
+#define DISPATCH64(KERNEL, SPLIT, GRID, ...)                                                      \
     do {                                                                                          \
         bool cnt = d.count_lookups != 0;                                                          \
         if (d.has_rot) {                                                                          \
-            if (cnt) KERNEL<true, false, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);                \
-            else KERNEL<true, false, false><<<GRID, 256, 0, st>>>(__VA_ARGS__);                   \
+            if (cnt) KERNEL<true, false, true, SPLIT><<<GRID, 256, 0, st>>>(__VA_ARGS__);         \
+            else KERNEL<true, false, false, SPLIT><<<GRID, 256, 0, st>>>(__VA_ARGS__);            \
         } else if (d.res_pow2) {                                                                  \
-            if (cnt) KERNEL<false, true, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);                \
-            else KERNEL<false, true, false><<<GRID, 256, 0, st>>>(__VA_ARGS__);                   \
+            if (cnt) KERNEL<false, true, true, SPLIT><<<GRID, 256, 0, st>>>(__VA_ARGS__);         \
+            else KERNEL<false, true, false, SPLIT><<<GRID, 256, 0, st>>>(__VA_ARGS__);            \
         } else {                                                                                  \
-            if (cnt) KERNEL<false, false, true><<<GRID, 256, 0, st>>>(__VA_ARGS__);               \
-            else KERNEL<false, false, false><<<GRID, 256, 0, st>>>(__VA_ARGS__);                  \
+            if (cnt) KERNEL<false, false, true, SPLIT><<<GRID, 256, 0, st>>>(__VA_ARGS__);        \
+            else KERNEL<false, false, false, SPLIT><<<GRID, 256, 0, st>>>(__VA_ARGS__);           \
         }                                                                                         \
     } while (0)
 
 void f110_launch_raycast64(const F110Dev &d, int env_begin, int env_count, int variant, cudaStream_t st)
 {
     long long warps = (long long)env_count * d.n_agents;
-    int grid = (int)((warps * 32 + 255) / 256);
-    if (grid == 0) return;
+    if (warps == 0) return;
+    const bool split = warps < F110_SPLIT_BELOW64 && !(variant & 128);
+    int grid = split ? (int)warps : (int)((warps * 32 + 255) / 256);
     const bool cnt = d.count_lookups != 0;
-#define RC64(R, P, MB, ALT)                                                                                \
-    do {                                                                                                 \
-        if (cnt) k_raycast64<R, P, true, 1><<<grid, 256, 0, st>>>(d, env_begin, env_count);              \
-        else if (variant & 8) k_raycast64<R, P, false, ALT><<<grid, 256, 0, st>>>(d, env_begin, env_count); \
-        else k_raycast64<R, P, false, MB><<<grid, 256, 0, st>>>(d, env_begin, env_count);                \
+#define RC64(R, P, MB, ALT)                                                                                         \
+    do {                                                                                                          \
+        if (split) {                                                                                              \
+            if (cnt) k_raycast64<R, P, true, 1, true><<<grid, 256, 0, st>>>(d, env_begin, env_count);             \
+            else k_raycast64<R, P, false, MB, true><<<grid, 256, 0, st>>>(d, env_begin, env_count);               \
+        } else if (cnt) k_raycast64<R, P, true, 1, false><<<grid, 256, 0, st>>>(d, env_begin, env_count);         \
+        else if (variant & 8) k_raycast64<R, P, false, ALT, false><<<grid, 256, 0, st>>>(d, env_begin, env_count); \
+        else k_raycast64<R, P, false, MB, false><<<grid, 256, 0, st>>>(d, env_begin, env_count);                  \
     } while (0)
     // registers per thread: 32 (8 CTAs per SM) where the kernel fits without spilling, else 40; variant bit 3 swaps the two
     if (d.has_rot) RC64(true, false, 6, 8);
@@ -466,9 +486,13 @@ void f110_launch_raycast64(const F110Dev &d, int env_begin, int env_count, int v
 
 void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, double *out, const int *order, int variant, cudaStream_t st)
 {
-    int grid = (int)(((long long)n * 32 + 255) / 256);
-    if (grid == 0) return;
-    DISPATCH64(k_scan_only64, grid, d, poses, n, out, order);
+    if (n <= 0) return;
+    if (n < F110_SPLIT_BELOW64 && !(variant & 128)) {
+        DISPATCH64(k_scan_only64, true, n, d, poses, n, out, order);
+    } else {
+        int grid = (int)(((long long)n * 32 + 255) / 256);
+        DISPATCH64(k_scan_only64, false, grid, d, poses, n, out, order);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
