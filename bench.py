@@ -152,6 +152,10 @@ def run_b200(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    numa_cpus = None
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:      # one process per GPU: host buffers on the GPU's own NUMA node
+        from red_gym_b200.host import bind_to_gpu_numa
+        numa_cpus = bind_to_gpu_numa(local)
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
     if world > 1:
@@ -262,7 +266,8 @@ def run_b200(args):
         e2e = {"value": float(n_envs) * agents * Ke * world / float(te.item()), "unit": "agent-steps/s",
                "h2d_bytes_per_step": act_h.numel() * 8 * world,
                "d2h_bytes_per_step": (obs_h.numel() * 8 + scans_h.numel() * scans_h.element_size() + done_h.numel()) * world,
-               "steps": Ke, "api": "f110_step_host (C ABI, pinned host buffers, full observation incl. scans copied back)"}
+               "steps": Ke, "api": "f110_step_host (C ABI, pinned host buffers, full observation incl. scans copied back)",
+               "host_numa_binding": "rank pinned to %d GPU-local CPUs" % len(numa_cpus) if numa_cpus else "none"}
         # informational: the same call with scans_host = NULL (scans stay in HBM for a device-side consumer such as the
         # bitmap rasteriser / a policy; poses, velocities, flags and done still come back every step)
         for _ in range(2):
