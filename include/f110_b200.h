@@ -124,6 +124,26 @@ int f110_set_map_image(f110_sim *sim, const uint8_t *free_px, int32_t h, int32_t
 /* get_dt alone, device to device: free_dev DEVICE [h][w] bytes -> edt_dev DEVICE [h][w] doubles (metres). */
 int f110_edt_build(const uint8_t *free_dev, int32_t h, int32_t w, double resolution, double *edt_dev, int device, void *stream);
 
+/* ---- The model functions of the step on their own, batched (what the reference exposes as
+ * f110_gym.envs.dynamic_models / collision_models and pins in its unit tests).  All pointers but params16 are DEVICE
+ * pointers on `device`; the calls are asynchronous on `stream`.  params16: host, the first 16 entries of the params
+ * vector (mu, C_Sf, C_Sr, lf, lr, h, m, I, s_min, s_max, sv_min, sv_max, v_switch, a_max, v_min, v_max). ----
+ * vehicle_dynamics_st (dynamic_models.py:123-176): x [n][7], u [n][2] (steering velocity, acceleration) -> f [n][7] */
+int f110_model_dynamics_st(const double *x_dev, const double *u_dev, const double *params16, int64_t n, double *f_dev,
+                           int device, void *stream);
+/* vehicle_dynamics_ks (dynamic_models.py:91-121): x [n][5], u [n][2] -> f [n][5] */
+int f110_model_dynamics_ks(const double *x_dev, const double *u_dev, const double *params16, int64_t n, double *f_dev,
+                           int device, void *stream);
+/* pid (dynamic_models.py:178-221): in [n][4] = speed, steer, current_speed, current_steer -> out [n][2] = accl, sv */
+int f110_model_pid(const double *in_dev, double max_sv, double max_a, double max_v, double min_v, int64_t n, double *out_dev,
+                   int device, void *stream);
+/* get_vertices (collision_models.py:238-260): poses [n][3] -> corners [n][4][2] (rl, rr, fr, fl) */
+int f110_model_vertices(const double *poses_dev, double length, double width, int64_t n, double *verts_dev, int device,
+                        void *stream);
+/* collision (GJK, collision_models.py:114-182): quads a, b [n][4][2] -> hit [n] bytes 0/1 */
+int f110_model_collision(const double *verts_a_dev, const double *verts_b_dev, int64_t n, uint8_t *hit_dev, int device,
+                         void *stream);
+
 /* Trig tables (laser_models.py:379-381, theta_dis entries) and per-beam tables
  * (base_classes.py:120-156, n_beams entries), computed by the host exactly as the reference does. */
 int f110_set_tables(f110_sim *sim, const double *sines, const double *cosines, const double *scan_angles,

@@ -25,7 +25,8 @@ EXPORTS = ["f110_last_error", "f110_abi_version", "f110_device_count", "f110_cre
            "f110_count_lookups", "f110_enable_timing", "f110_last_raycast_ms", "f110_launch_count", "f110_synchronize",
            "f110_bitmap_create", "f110_bitmap_destroy", "f110_bitmap_render",
            "f110_pursuit_create", "f110_pursuit_destroy", "f110_pursuit_plan",
-           "f110_render_create", "f110_render_destroy", "f110_render_frame"]
+           "f110_render_create", "f110_render_destroy", "f110_render_frame",
+           "f110_model_dynamics_st", "f110_model_dynamics_ks", "f110_model_pid", "f110_model_vertices", "f110_model_collision"]
 BITMAP_MODES = {"FILL": 0, "POLYGON": 1, "RAYS": 2}
 
 
@@ -108,6 +109,11 @@ def load():
     L.f110_render_create.argtypes = [ctypes.POINTER(RenderConfig), vp, ctypes.c_int, ctypes.POINTER(vp)]
     L.f110_render_destroy.argtypes = [vp]
     L.f110_render_frame.argtypes = [vp, vp, vp, vp, i64, vp, vp]
+    L.f110_model_dynamics_st.argtypes = [vp, vp, vp, i64, vp, ctypes.c_int, vp]
+    L.f110_model_dynamics_ks.argtypes = [vp, vp, vp, i64, vp, ctypes.c_int, vp]
+    L.f110_model_pid.argtypes = [vp, f64, f64, f64, f64, i64, vp, ctypes.c_int, vp]
+    L.f110_model_vertices.argtypes = [vp, f64, f64, i64, vp, ctypes.c_int, vp]
+    L.f110_model_collision.argtypes = [vp, vp, i64, vp, ctypes.c_int, vp]
     for name in EXPORTS:
         fn = getattr(L, name)
         if name not in ("f110_last_error", "f110_launch_count"):

@@ -103,6 +103,7 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
     if (cfg->abi_version != F110_ABI_VERSION) return fail(F110_ERR_INVALID, "abi_version %d != %d", cfg->abi_version, F110_ABI_VERSION);
     if (cfg->n_envs < 1 || cfg->n_agents < 1 || cfg->n_agents > F110_MAX_AGENTS || cfg->n_beams < 2 || cfg->theta_dis < 1)
         return fail(F110_ERR_INVALID, "bad sizes: n_envs=%d n_agents=%d n_beams=%d", cfg->n_envs, cfg->n_agents, cfg->n_beams);
+    if (cfg->n_beams > 65535) return fail(F110_ERR_INVALID, "n_beams=%d: at most 65535 beams per scan", cfg->n_beams);
     if (cfg->integrator != F110_INTEGRATOR_RK4 && cfg->integrator != F110_INTEGRATOR_EULER)
         return fail(F110_ERR_INVALID, "Invalid Integrator Specified (%d)", cfg->integrator);
     if (cfg->ego_idx < 0 || cfg->ego_idx >= cfg->n_agents) return fail(F110_ERR_INVALID, "ego_idx out of range");
@@ -384,6 +385,70 @@ extern "C" int f110_edt_build(const uint8_t *free_dev, int32_t h, int32_t w, dou
     cudaFree(g);
     if (e != cudaSuccess || e2 != cudaSuccess) return fail(F110_ERR_CUDA, "EDT kernels failed: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
     return F110_OK;
+}
+
+// ---- model functions on their own (device pointers on `device`; asynchronous on `stream`) ----
+static int model_device(int device)
+{
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(F110_ERR_CUDA, "no CUDA device available; this library has no CPU path");
+    }
+    if (device < 0 || device >= ndev) return fail(F110_ERR_INVALID, "device %d out of range (%d devices)", device, ndev);
+    CK(cudaSetDevice(device));
+    return F110_OK;
+}
+static int model_done(const char *what)
+{
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(F110_ERR_CUDA, "%s failed: %s", what, cudaGetErrorString(e));
+    return F110_OK;
+}
+extern "C" int f110_model_dynamics_st(const double *x_dev, const double *u_dev, const double *params16, int64_t n, double *f_dev,
+                                      int device, void *stream)
+{
+    if (!x_dev || !u_dev || !params16 || !f_dev || n < 0) return fail(F110_ERR_INVALID, "bad arguments");
+    int rc = model_device(device);
+    if (rc) return rc;
+    f110_launch_model_dynamics(x_dev, u_dev, params16, n, 0, f_dev, (cudaStream_t)stream);
+    return model_done("vehicle_dynamics_st");
+}
+extern "C" int f110_model_dynamics_ks(const double *x_dev, const double *u_dev, const double *params16, int64_t n, double *f_dev,
+                                      int device, void *stream)
+{
+    if (!x_dev || !u_dev || !params16 || !f_dev || n < 0) return fail(F110_ERR_INVALID, "bad arguments");
+    int rc = model_device(device);
+    if (rc) return rc;
+    f110_launch_model_dynamics(x_dev, u_dev, params16, n, 1, f_dev, (cudaStream_t)stream);
+    return model_done("vehicle_dynamics_ks");
+}
+extern "C" int f110_model_pid(const double *in_dev, double max_sv, double max_a, double max_v, double min_v, int64_t n, double *out_dev,
+                              int device, void *stream)
+{
+    if (!in_dev || !out_dev || n < 0) return fail(F110_ERR_INVALID, "bad arguments");
+    int rc = model_device(device);
+    if (rc) return rc;
+    f110_launch_model_pid(in_dev, max_sv, max_a, max_v, min_v, n, out_dev, (cudaStream_t)stream);
+    return model_done("pid");
+}
+extern "C" int f110_model_vertices(const double *poses_dev, double length, double width, int64_t n, double *verts_dev, int device,
+                                   void *stream)
+{
+    if (!poses_dev || !verts_dev || n < 0) return fail(F110_ERR_INVALID, "bad arguments");
+    int rc = model_device(device);
+    if (rc) return rc;
+    f110_launch_model_vertices(poses_dev, length, width, n, verts_dev, (cudaStream_t)stream);
+    return model_done("get_vertices");
+}
+extern "C" int f110_model_collision(const double *verts_a_dev, const double *verts_b_dev, int64_t n, uint8_t *hit_dev, int device,
+                                    void *stream)
+{
+    if (!verts_a_dev || !verts_b_dev || !hit_dev || n < 0) return fail(F110_ERR_INVALID, "bad arguments");
+    int rc = model_device(device);
+    if (rc) return rc;
+    f110_launch_model_collision(verts_a_dev, verts_b_dev, n, hit_dev, (cudaStream_t)stream);
+    return model_done("collision");
 }
 
 extern "C" int f110_set_tables(f110_sim *s, const double *sines, const double *cosines, const double *scan_angles,

@@ -88,3 +88,9 @@ void f110_launch_edt32(const double *src, float *dst, size_t cells, double inv_r
 void f110_launch_order(const F110Dev &d, cudaStream_t st);      // (chunk, tile, heading) counting sort -> d.order
 void f110_launch_order_poses(const F110Dev &d, const double *poses, int n, int *buf, cudaStream_t st);
 void f110_launch_pad_edt32(const float *src, float *dst, int h, int w, int pad, float oob, cudaStream_t st);
+
+// model functions on their own (f110_kernels_fp64.cu, end of file)
+void f110_launch_model_dynamics(const double *x, const double *u, const double *p16, long long n, int ks, double *f, cudaStream_t st);
+void f110_launch_model_pid(const double *in, double max_sv, double max_a, double max_v, double min_v, long long n, double *out, cudaStream_t st);
+void f110_launch_model_vertices(const double *poses, double length, double width, long long n, double *verts, cudaStream_t st);
+void f110_launch_model_collision(const double *a, const double *b, long long n, uint8_t *hit, cudaStream_t st);

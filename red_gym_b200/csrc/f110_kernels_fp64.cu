@@ -83,6 +83,20 @@ static __device__ __forceinline__ void dynamics_st(const double x[7], double sv_
     }
 }
 
+// pid (dynamic_models.py:178-221): speed / steer set points -> acceleration, steering velocity
+static __device__ __forceinline__ void pid_ctrl(double speed, double steer, double cur_speed, double cur_steer, double max_sv,
+                                                double max_a, double max_v, double min_v, double &accl, double &sv)
+{
+    double steer_diff = steer - cur_steer;
+    if (fabs(steer_diff) > 1e-4) sv = (steer_diff / fabs(steer_diff)) * max_sv;
+    else sv = 0.0;
+    double vel_diff = speed - cur_speed;
+    double kp;
+    if (cur_speed > 0.) kp = (vel_diff > 0) ? 10.0 * max_a / max_v : 10.0 * max_a / (-min_v);
+    else kp = (vel_diff > 0) ? 2.0 * max_a / max_v : 2.0 * max_a / (-min_v);
+    accl = kp * vel_diff;
+}
+
 static __device__ __forceinline__ unsigned pool_index(int e, long long episode, int n_pool)
 {
     unsigned long long z = (unsigned long long)e * 0x9E3779B97F4A7C15ull + (unsigned long long)episode * 0xBF58476D1CE4E5B9ull;
@@ -136,18 +150,8 @@ __global__ void __launch_bounds__(128) k_dynamics(const F110Dev d)
     const double *pp = d.params + F110_NP * a;
     VehP p = { pp[0], pp[1], pp[2], pp[3], pp[4], pp[5], pp[6], pp[7], pp[8], pp[9], pp[10], pp[11], pp[12], pp[13], pp[14], pp[15] };
 
-    // pid (dynamic_models.py:178-221)
     double sv, accl;
-    {
-        double steer_diff = steer - x[2];
-        if (fabs(steer_diff) > 1e-4) sv = (steer_diff / fabs(steer_diff)) * p.sv_max;
-        else sv = 0.0;
-        double vel_diff = vel_cmd - x[3];
-        double kp;
-        if (x[3] > 0.) kp = (vel_diff > 0) ? 10.0 * p.a_max / p.v_max : 10.0 * p.a_max / (-p.v_min);
-        else kp = (vel_diff > 0) ? 2.0 * p.a_max / p.v_max : 2.0 * p.a_max / (-p.v_min);
-        accl = kp * vel_diff;
-    }
+    pid_ctrl(vel_cmd, steer, x[3], x[2], p.sv_max, p.a_max, p.v_max, p.v_min, accl, sv);
 
     const double dt = d.timestep;
     if (d.integrator == 1) {   // RK4 (base_classes.py:282-371)
@@ -943,4 +947,88 @@ __global__ void k_edt32(const double *__restrict__ src, float *__restrict__ dst,
 void f110_launch_edt32(const double *src, float *dst, size_t cells, double inv_res, double eps, float cap, float sent, cudaStream_t st)
 {
     k_edt32<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(src, dst, cells, inv_res, eps, cap, sent);
+}
+
+// ------------------------------------------------------------------------------------------------
+// The model functions of the step on their own (dynamic_models.py, collision_models.py), batched: what the reference
+// exposes as f110_gym.envs.dynamic_models / collision_models and pins in its unit tests (f_st_gt, GJK known answers).
+// They call the very device functions the step kernels use.
+// ------------------------------------------------------------------------------------------------
+// vehicle_dynamics_st (:123-176), x [n][7], u [n][2] -> f [n][7]; ks = 1: vehicle_dynamics_ks (:91-121), 5 states
+__global__ void __launch_bounds__(128) k_model_dynamics(const double *__restrict__ x, const double *__restrict__ u, VehP p,
+                                                        long long n, int ks, double *__restrict__ f)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (ks) {
+        const double *xi = x + 5 * i;
+        double u0 = steering_constraint(xi[2], u[2 * i], p.s_min, p.s_max, p.sv_min, p.sv_max);
+        double u1 = accl_constraints(xi[3], u[2 * i + 1], p.v_switch, p.a_max, p.v_min, p.v_max);
+        double s4, c4;
+        sincos(xi[4], &s4, &c4);
+        double *fi = f + 5 * i;
+        fi[0] = xi[3] * c4; fi[1] = xi[3] * s4; fi[2] = u0; fi[3] = u1; fi[4] = xi[3] / (p.lf + p.lr) * tan(xi[2]);
+        return;
+    }
+    double xs[7], fs[7];
+#pragma unroll
+    for (int k = 0; k < 7; k++) xs[k] = x[7 * i + k];
+    dynamics_st(xs, u[2 * i], u[2 * i + 1], p, fs);
+#pragma unroll
+    for (int k = 0; k < 7; k++) f[7 * i + k] = fs[k];
+}
+// pid (:178-221): in [n][4] = speed, steer, current_speed, current_steer -> out [n][2] = accl, sv
+__global__ void __launch_bounds__(128) k_model_pid(const double *__restrict__ in, double max_sv, double max_a, double max_v, double min_v,
+                                                   long long n, double *__restrict__ out)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double accl, sv;
+    pid_ctrl(in[4 * i], in[4 * i + 1], in[4 * i + 2], in[4 * i + 3], max_sv, max_a, max_v, min_v, accl, sv);
+    out[2 * i] = accl; out[2 * i + 1] = sv;
+}
+// get_vertices (collision_models.py:238-260): poses [n][3] -> corners [n][4][2]
+__global__ void __launch_bounds__(128) k_model_vertices(const double *__restrict__ poses, double length, double width, long long n,
+                                                        double *__restrict__ verts)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double v[4][2];
+    get_vertices(poses[3 * i], poses[3 * i + 1], poses[3 * i + 2], length, width, v);
+#pragma unroll
+    for (int k = 0; k < 4; k++) { verts[8 * i + 2 * k] = v[k][0]; verts[8 * i + 2 * k + 1] = v[k][1]; }
+}
+// collision (GJK, :114-182): quads a, b [n][4][2] -> hit [n]
+__global__ void __launch_bounds__(128) k_model_collision(const double *__restrict__ a, const double *__restrict__ b, long long n,
+                                                         uint8_t *__restrict__ hit)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double va[4][2], vb[4][2];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        va[k][0] = a[8 * i + 2 * k]; va[k][1] = a[8 * i + 2 * k + 1];
+        vb[k][0] = b[8 * i + 2 * k]; vb[k][1] = b[8 * i + 2 * k + 1];
+    }
+    hit[i] = gjk_collision(va, vb) ? 1 : 0;
+}
+
+void f110_launch_model_dynamics(const double *x, const double *u, const double *p16, long long n, int ks, double *f, cudaStream_t st)
+{
+    if (n <= 0) return;
+    VehP p = { p16[0], p16[1], p16[2], p16[3], p16[4], p16[5], p16[6], p16[7], p16[8], p16[9], p16[10], p16[11], p16[12], p16[13],
+               p16[14], p16[15] };
+    k_model_dynamics<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(x, u, p, n, ks, f);
+}
+void f110_launch_model_pid(const double *in, double max_sv, double max_a, double max_v, double min_v, long long n, double *out, cudaStream_t st)
+{
+    if (n > 0) k_model_pid<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(in, max_sv, max_a, max_v, min_v, n, out);
+}
+void f110_launch_model_vertices(const double *poses, double length, double width, long long n, double *verts, cudaStream_t st)
+{
+    if (n > 0) k_model_vertices<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(poses, length, width, n, verts);
+}
+void f110_launch_model_collision(const double *a, const double *b, long long n, uint8_t *hit, cudaStream_t st)
+{
+    if (n > 0) k_model_collision<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(a, b, n, hit);
 }
