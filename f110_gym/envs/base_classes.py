@@ -28,7 +28,7 @@ class Simulator(object):
         self.integrator = integrator
         self.agent_poses = np.empty((self.num_agents, 3))
         self.collisions = np.zeros((self.num_agents, ))
-        self.collision_idx = -1 * np.ones((self.num_agents, ))
+        self._collision_idx = -1 * np.ones((self.num_agents, ))
         self._device = device
         self._batch = None
         if map_path is not None:
@@ -62,7 +62,7 @@ class Simulator(object):
         A = self.num_agents
         self.agent_poses = np.stack([o[0], o[1], o[4]], axis=1)
         self.collisions = o[7].copy()
-        self.collision_idx = self._batch.collision_idx.cpu().numpy()[0] if A > 1 else -1 * np.ones((A,))
+        self._collision_idx = None if A > 1 else -1 * np.ones((A,))      # A > 1: fetched from the device on access
         scans = self._h_scans.numpy()
         observations = {'ego_idx': self.ego_idx,
                         'scans': [scans[i].copy() for i in range(A)],
@@ -77,6 +77,13 @@ class Simulator(object):
         self.lap_counts = o[9].copy()
         self.done = bool(self._h_done[0])
         return observations
+
+    @property
+    def collision_idx(self):
+        """collision_multiple's partner index per agent (collision_models.py:197), -1 if none."""
+        if self._collision_idx is None:
+            self._collision_idx = self._batch.collision_idx.cpu().numpy()[0]
+        return self._collision_idx
 
     def step(self, control_inputs):
         if self._batch is None:

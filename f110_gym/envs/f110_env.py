@@ -54,7 +54,7 @@ class F110Env(_Base):
         self.lap_times = np.zeros((self.num_agents, ))
         self.lap_counts = np.zeros((self.num_agents, ))
         self.current_time = 0.0
-        self.toggle_list = np.zeros((self.num_agents,))
+        self._toggles = np.zeros((self.num_agents,))
         self.start_xs = np.zeros((self.num_agents, ))
         self.start_ys = np.zeros((self.num_agents, ))
         self.start_thetas = np.zeros((self.num_agents, ))
@@ -77,10 +77,21 @@ class F110Env(_Base):
         self.poses_y = obs['poses_y']
         self.poses_theta = obs['poses_theta']
         self.collisions = obs['collisions']
-        self.toggle_list = self.sim._batch.toggle_list.cpu().numpy()[0].astype(np.float64)
+        self._toggles = None                  # read back from the device only if somebody looks (toggle_list below)
         done = self.sim.done
-        info = {'checkpoint_done': self.toggle_list >= 4}
+        info = {'checkpoint_done': self.lap_counts >= 2}      # toggle_list >= 4 (f110_env.py:299); lap_counts = toggles // 2
         return obs, self.timestep, bool(done), info
+
+    @property
+    def toggle_list(self):
+        """Start-line toggles per agent (f110_env.py:183, 233-240), kept on the device; fetched on access."""
+        if self._toggles is None:
+            self._toggles = self.sim._batch.toggle_list.cpu().numpy()[0].astype(np.float64)
+        return self._toggles
+
+    @toggle_list.setter
+    def toggle_list(self, value):
+        self._toggles = np.asarray(value, dtype=np.float64)
 
     def step(self, action):
         obs = self.sim.step(action)
