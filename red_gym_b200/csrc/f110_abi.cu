@@ -126,6 +126,9 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
     memset(&d, 0, sizeof(d));
     const size_t N = cfg->n_envs, A = cfg->n_agents, NA = N * A, B = cfg->n_beams;
     d.n_envs = cfg->n_envs; d.n_agents = cfg->n_agents; d.n_beams = cfg->n_beams; d.integrator = cfg->integrator;
+    d.n_sm = 148;
+    cudaDeviceGetAttribute(&d.n_sm, cudaDevAttrMultiProcessorCount, device);
+    if (d.n_sm < 1) d.n_sm = 1;
     d.ego_idx = cfg->ego_idx; d.theta_dis = cfg->theta_dis; d.noise_mode = cfg->noise_mode; d.auto_reset = cfg->auto_reset;
     d.scan_is_f32 = cfg->precision == F110_PRECISION_FP32;
     d.env_offset = cfg->env_offset;

@@ -12,12 +12,19 @@ enum { F110_P_MU, F110_P_CSF, F110_P_CSR, F110_P_LF, F110_P_LR, F110_P_H, F110_P
 // one warp per scan would leave most of the GPU waiting on ~365 dependent gathers in a row.  Measured per step,
 // split / one warp per scan: fp64 256 envs 0.073 / 0.138 ms, 4096 envs 0.142 / 0.173, 8192 envs 0.221 / 0.196;
 // fp32 256 envs 0.061 / 0.095, 4096 envs 0.127 / 0.123, 8192 envs 0.193 / 0.139.  Variant bit 7 turns it off.
+// Split launches map CTA b to scan (b % n_sm) * ceil(n / n_sm) + b / n_sm: CTAs are handed to the SMs round-robin,
+// so the CTAs resident on one SM then hold consecutive scans (neighbours on the track, overlapping EDT footprints)
+// instead of scans n_sm apart (worth 2 % at 4096 scans: what holds the split kernels back is the CTA-wide wait for the
+// slowest of the 8 warps, ncu stall_barrier 18.8, not the L1 hit rate).  The grid is n_sm * ceil(n / n_sm) CTAs; the surplus ones exit.
+static __host__ __device__ __forceinline__ int f110_split_grid(int n, int n_sm) { return n_sm * ((n + n_sm - 1) / n_sm); }
+static __device__ __forceinline__ int f110_split_scan(int b, int n, int n_sm) { return (b % n_sm) * ((n + n_sm - 1) / n_sm) + b / n_sm; }
 #define F110_SPLIT_BELOW64 6144
 #define F110_SPLIT_BELOW32 3072
 
 struct F110Dev {
     int n_envs, n_agents, n_beams, integrator, ego_idx, theta_dis;
     int noise_mode, auto_reset, count_lookups, n_pool, scan_is_f32, env_offset;
+    int n_sm, pad0_;                   // SMs of the device (split-scan CTA -> scan mapping)
     double timestep, fov, eps, max_range, theta_inc, ttc_thresh, noise_std;
     unsigned long long seed;
     unsigned long long inc_fix;        // theta_inc in 32.32 fixed point; kstep = 32 * inc_fix (one round of 32 beams)

@@ -382,7 +382,7 @@ template <bool ROT, bool POW2, bool COUNT, int MINB, bool SPLIT>
 __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int env_begin, int env_count)
 {
     const int NA = d.n_envs * d.n_agents;
-    int w = SPLIT ? (int)blockIdx.x : (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    int w = SPLIT ? f110_split_scan((int)blockIdx.x, env_count * d.n_agents, d.n_sm) : (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (w >= env_count * d.n_agents) return;
     int ia = env_begin * d.n_agents + w;
     if (d.order) ia = d.order[ia];      // spatial launch order (f110_order.cu)
@@ -430,7 +430,7 @@ template <bool ROT, bool POW2, bool COUNT, bool SPLIT>
 __global__ void __launch_bounds__(256) k_scan_only64(const F110Dev d, const double *__restrict__ poses, int n,
                                                      double *__restrict__ out, const int *__restrict__ order)
 {
-    int w = SPLIT ? (int)blockIdx.x : (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    int w = SPLIT ? f110_split_scan((int)blockIdx.x, n, d.n_sm) : (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (w >= n) return;
     if (order) w = order[w];
     bool hit = false;
@@ -470,7 +470,7 @@ void f110_launch_raycast64(const F110Dev &d, int env_begin, int env_count, int v
     long long warps = (long long)env_count * d.n_agents;
     if (warps == 0) return;
     const bool split = warps < F110_SPLIT_BELOW64 && !(variant & 128);
-    int grid = split ? (int)warps : (int)((warps * 32 + 255) / 256);
+    int grid = split ? f110_split_grid((int)warps, d.n_sm) : (int)((warps * 32 + 255) / 256);
     const bool cnt = d.count_lookups != 0;
 #define RC64(R, P, MB, ALT)                                                                                         \
     do {                                                                                                          \
@@ -492,7 +492,7 @@ void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, doubl
 {
     if (n <= 0) return;
     if (n < F110_SPLIT_BELOW64 && !(variant & 128)) {
-        DISPATCH64(k_scan_only64, true, n, d, poses, n, out, order);
+        DISPATCH64(k_scan_only64, true, f110_split_grid(n, d.n_sm), d, poses, n, out, order);
     } else {
         int grid = (int)(((long long)n * 32 + 255) / 256);
         DISPATCH64(k_scan_only64, false, grid, d, poses, n, out, order);
