@@ -89,7 +89,11 @@ static __device__ __forceinline__ bool line_setup(int w, int h, int ax, int ay, 
 static __device__ __forceinline__ void line_span(unsigned *mask, int wpr, const LineJob &j, int i0, int i1)
 {
     if (i0 >= i1) return;
-    int m = (i0 > 0 && j.dx > 0) ? (int)((2ll * j.dy * i0 + j.dx - 1) / (2ll * j.dx)) : 0;
+    int m = 0;
+    if (i0 > 0 && j.dx > 0) {
+        if (j.dx < 16384) m = (2 * j.dy * i0 + j.dx - 1) / (2 * j.dx);      // dy <= dx, i0 <= dx: below 2^30
+        else m = (int)((2ll * j.dy * i0 + j.dx - 1) / (2ll * j.dx));
+    }
     int err = j.dx - 2 * j.dy * (i0 + 1) + 2 * j.dx * m;
     for (int i = i0; i < i1; i++) {
         if (j.vert) set_px(mask, wpr, j.px + m, j.py + j.sy * i);
@@ -125,7 +129,11 @@ static __device__ __forceinline__ bool edge_setup(int w, int h, int p0x, int p0y
         c0x = q0x; c1x = q1x;                                   // x always from the clipped end points,
         if (q0y != q1y) { c0y = q0y; c1y = q1y; }               // y only when the clipped piece spans rows
     }
-    e.dx = ((c1x - c0x) * XY_ONE) / (c1y - c0y);                // C division: truncates, like the reference
+    {   // C division: truncates, like the reference; 32-bit when the operands fit (a 64-bit division is ~4x the instructions)
+        const long long ddx = c1x - c0x, ddy = c1y - c0y;
+        if (ddx > -32768 && ddx < 32768 && ddy > -32768 && ddy < 32768) e.dx = (long long)(((int)ddx * XY_ONE) / (int)ddy);
+        else e.dx = (ddx * XY_ONE) / ddy;
+    }
     int y0, y1;
     long long x;
     if (p0y < p1y) { y0 = p0y; y1 = p1y; x = c0x * XY_ONE + (p0y - c0y) * e.dx; }
@@ -185,10 +193,11 @@ __global__ void __launch_bounds__(256, 4) k_lidar_bitmap(const F110BitmapDev d, 
             pts[t] = make_int2((int)rint((double)d.cx + sd * d.cosa[t]), (int)rint((double)d.cy + sd * d.sina[t]));
         }
         for (int i = tid; i < 3 * H * wpr + H; i += nt) mask[i] = 0u;
-        if (tid == 0) *qn = 0u;
+        if (tid == 0) { qn[0] = 0u; qn[1] = 0u; }     // queue fill, next unclaimed point of pass 1
         __syncthreads();
-        // pass 1: one thread per line / edge; short ones are finished here, long ones queued
-        for (int t = tid; t < T; t += nt) {
+        // pass 1: one thread per line / edge, claimed one at a time (their cost varies: clipping, 0-12 pixels / rows);
+        // short ones are finished here, long ones queued
+        for (int t = (int)atomicAdd(qn + 1, 1u); t < T; t = (int)atomicAdd(qn + 1, 1u)) {
             const int2 p1 = pts[t];
             const int2 p0 = rays ? make_int2(d.cx, d.cy) : pts[t ? t - 1 : T - 1];
             LineJob lj;
