@@ -206,7 +206,9 @@ template <bool POW2>
 static __device__ __forceinline__ int cell_index(double v, const F110Dev &d)
 {
     if (POW2) return __double2loint(__dadd_rz(v, d.magic64));
-    double t = __dadd_rz(v * d.inv_res, 4194304.0);
+    // one fused instruction: the exact product plus 2^22, truncated.  Where that differs from truncating the ROUNDED
+    // product (the last of the 30 fraction bits, rarely) the value is inside the redo band below anyway.
+    double t = __fma_rz(v, d.inv_res, 4194304.0);
     unsigned lo = (unsigned)__double2loint(t), hi = (unsigned)__double2hiint(t);
     int c = (int)(__funnelshift_l(lo, hi, 2) & 0x3FFFFFu);
     if (((lo + 2u) & 0x3FFFFFFFu) < 4u) c = (int)__ddiv_rn(v, d.res);
