@@ -9,9 +9,10 @@ enum { F110_P_MU, F110_P_CSF, F110_P_CSR, F110_P_LF, F110_P_LR, F110_P_H, F110_P
        F110_P_WIDTH, F110_P_LENGTH, F110_NP };
 
 // Launches of fewer scans than this give each scan a CTA of 8 warps instead of one warp (k_*split / SPLIT = true):
-// one warp per scan would leave most of the GPU waiting on ~365 dependent gathers in a row.  Measured per step,
-// split / one warp per scan: fp64 256 envs 0.073 / 0.138 ms, 4096 envs 0.142 / 0.173, 8192 envs 0.221 / 0.196;
-// fp32 256 envs 0.061 / 0.095, 4096 envs 0.127 / 0.123, 8192 envs 0.193 / 0.139.  Variant bit 7 turns it off.
+// one warp per scan would leave most of the GPU waiting on ~365 dependent gathers in a row.  The warps of the CTA
+// claim rounds of 32 beams from a shared counter.  Measured per step, split / one warp per scan: fp64 256 envs
+// 0.069 / 0.138 ms, 2048 envs 0.090 / 0.12, 4096 envs 0.129 / 0.173, 8192 envs 0.22 / 0.196; fp32 256 envs
+// 0.053 / 0.095, 2048 envs 0.082 / 0.10, 4096 envs 0.127 / 0.123, 8192 envs 0.193 / 0.139.  Variant bit 7 turns it off.
 // Split launches map CTA b to scan (b % n_sm) * ceil(n / n_sm) + b / n_sm: CTAs are handed to the SMs round-robin,
 // so the CTAs resident on one SM then hold consecutive scans (neighbours on the track, overlapping EDT footprints)
 // instead of scans n_sm apart (worth 2 % at 4096 scans: what holds the split kernels back is the CTA-wide wait for the

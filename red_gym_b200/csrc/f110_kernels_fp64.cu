@@ -354,26 +354,48 @@ static __device__ __forceinline__ bool ttc_hit(double range, double side, double
 // One warp per scan, 32 consecutive beams in lockstep per round (adjacent beams hit adjacent EDT
 // cells, so a warp-level gather touches few cache lines); lanes whose ray has converged idle until
 // the round's slowest ray is done.
-// A scan may also be split over the `stride` warps of a CTA (warp r0 takes rounds r0, r0 + stride, ...): below
-// ~32 768 scans one warp per scan leaves the GPU waiting on 365 dependent gathers in a row per warp.
+// A scan may also be split over the warps of a CTA: below a few thousand scans one warp per scan leaves the GPU waiting
+// on 365 dependent gathers in a row per warp.  The warps then claim rounds one at a time from a shared counter
+// (`next`): rounds differ in length, and the CTA ends with its slowest warp.
 template <bool ROT, bool POW2, bool STEP, bool COUNT>
-static __device__ __forceinline__ void scan_rounds(const F110Dev &d, const Scan64 *c, bool &hit_any, unsigned &nlook,
-                                                   int r0 = 0, int stride = 1)
+static __device__ __forceinline__ void scan_beam(const F110Dev &d, const Scan64 *c, int i, double a, bool &hit_any, unsigned &nlook)
+{
+    int ti = theta_index_of(d, c, i, a);
+    double rng = trace_ray<ROT, POW2, COUNT>(d, c, ti, nlook);
+    const double *np_ = c->noise;
+    if (np_) rng += __ldg(np_ + i);
+    c->out[i] = rng;
+    if (STEP && rng < c->r_gate)
+        hit_any |= ttc_hit(rng, __ldg(d.side_dist + i), c->vel, __ldg(d.beam_cos + i), d.ttc_thresh);
+}
+
+// a = closed-form beam index t0 + i*inc (theta_index_of replays the reference's running sum where it matters)
+template <bool ROT, bool POW2, bool STEP, bool COUNT>
+static __device__ __forceinline__ void scan_rounds(const F110Dev &d, const Scan64 *c, bool &hit_any, unsigned &nlook)
 {
     const int lane = threadIdx.x & 31;
-    if (COUNT) nlook += (lane == 0 && r0 == 0);
-    // closed-form beam index t0 + i*inc, carried per lane
-    double a = c->t0 + (double)(lane + 32 * r0) * d.theta_inc;
-    const double a_step = (double)(32 * stride) * d.theta_inc;
-    for (int i = lane + 32 * r0; i < d.n_beams; i += 32 * stride) {
-        int ti = theta_index_of(d, c, i, a);
-        double r = trace_ray<ROT, POW2, COUNT>(d, c, ti, nlook);
-        const double *np_ = c->noise;
-        if (np_) r += __ldg(np_ + i);
-        c->out[i] = r;
-        if (STEP && r < c->r_gate)
-            hit_any |= ttc_hit(r, __ldg(d.side_dist + i), c->vel, __ldg(d.beam_cos + i), d.ttc_thresh);
-        a += a_step;
+    if (COUNT) nlook += (lane == 0);
+    double a = c->t0 + (double)lane * d.theta_inc;
+    for (int i = lane; i < d.n_beams; i += 32) {
+        scan_beam<ROT, POW2, STEP, COUNT>(d, c, i, a, hit_any, nlook);
+        a += 32.0 * d.theta_inc;
+    }
+}
+
+// the CTA-per-scan version: warps claim rounds from `next`
+template <bool ROT, bool POW2, bool STEP, bool COUNT>
+static __device__ __forceinline__ void scan_rounds_claimed(const F110Dev &d, const Scan64 *c, bool &hit_any, unsigned &nlook, int *next)
+{
+    const int lane = threadIdx.x & 31;
+    if (COUNT) nlook += (threadIdx.x == 0);
+    const int rounds = (d.n_beams + 31) >> 5;
+    for (;;) {
+        int r = 0;
+        if (lane == 0) r = atomicAdd(next, 1);
+        r = __shfl_sync(FULL, r, 0);
+        if (r >= rounds) break;
+        const int i = lane + 32 * r;
+        if (i < d.n_beams) scan_beam<ROT, POW2, STEP, COUNT>(d, c, i, c->t0 + (double)i * d.theta_inc, hit_any, nlook);
     }
 }
 
@@ -405,9 +427,11 @@ __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int en
     Scan64 *c = rows + (SPLIT ? 0 : (threadIdx.x >> 5));
     if (!SPLIT || threadIdx.x < 32)
         scan_setup64<ROT, POW2, true>(d, px, py, yaw, vel, (double *)d.scans + (size_t)ia * d.n_beams, noise_row, c);
+    __shared__ int next_round;
     if (SPLIT) {
+        if (threadIdx.x == 0) next_round = 0;
         __syncthreads();                        // one row for the CTA, written by its first warp
-        scan_rounds<ROT, POW2, true, COUNT>(d, c, hit, nlook, threadIdx.x >> 5, 8);
+        scan_rounds_claimed<ROT, POW2, true, COUNT>(d, c, hit, nlook, &next_round);
         hit = __syncthreads_or(hit) != 0;       // every warp has read the state by now (the returns above are per CTA)
     } else {
         scan_rounds<ROT, POW2, true, COUNT>(d, c, hit, nlook);
@@ -441,8 +465,10 @@ __global__ void __launch_bounds__(256) k_scan_only64(const F110Dev d, const doub
     Scan64 *c = rows + (SPLIT ? 0 : (threadIdx.x >> 5));
     if (!SPLIT || threadIdx.x < 32)
         scan_setup64<ROT, POW2, false>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], 0.0, out + (size_t)w * d.n_beams, nullptr, c);
+    __shared__ int next_round;
+    if (SPLIT && threadIdx.x == 0) next_round = 0;
     if (SPLIT) __syncthreads();
-    if (SPLIT) scan_rounds<ROT, POW2, false, COUNT>(d, c, hit, nlook, threadIdx.x >> 5, 8);
+    if (SPLIT) scan_rounds_claimed<ROT, POW2, false, COUNT>(d, c, hit, nlook, &next_round);
     else scan_rounds<ROT, POW2, false, COUNT>(d, c, hit, nlook);
     if (COUNT) {
 #pragma unroll
