@@ -348,3 +348,39 @@ def test_small_batch_split_scans_do_not_change_results(dtype, agents):
     assert a_env.lookups() == b_env.lookups() and torch.equal(a_env.scans, b_env.scans)
     p = np.concatenate([poses[:, 0], [[3.0, 4.0, 0.3]]])
     assert torch.equal(a_env.raycast(p), b_env.raycast(p))
+
+
+def test_full_size_config3_matches_small_batches_of_the_same_envs():
+    """BASELINE config 3 at its full size (2^20 envs, fp32 fast path, Philox noise, auto-reset; spatially ordered launch,
+    one warp per scan) against two small handles that own slices of the same global env range (CTA-per-scan kernels, no
+    ordering): a scan, a state and a flag must not depend on the batch an env was stepped in.  Plus the invariants of the
+    whole batch: ranges inside [0, max_range] up to noise, nothing non-finite, counters consistent."""
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    import torch
+    N, T = 1 << 20, 250
+    pool = raceline_poses(4096)[:, None, :]
+    poses = raceline_poses(N)[:, None, :]
+    kw = dict(num_agents=1, map=os.path.join(MAPS, "example_map"), dtype="fp32", noise="philox", auto_reset=True, reset_poses=pool)
+    whole = BatchF110Env(num_envs=N, **kw)
+    parts = [(b, c, BatchF110Env(num_envs=c, env_offset=b, **kw)) for b, c in ((0, 2048), (777_000, 1500))]
+    whole.reset(poses)
+    for b, c, e in parts:
+        e.reset(poses[b:b + c])
+    g = torch.Generator(device="cuda").manual_seed(11)
+    for t in range(T):
+        act = torch.rand((N, 1, 2), generator=g, device="cuda", dtype=torch.float64)
+        act[..., 0] = (act[..., 0] * 2 - 1) * 0.4189
+        act[..., 1] = act[..., 1] * 8.0
+        whole.step(act)
+        for b, c, e in parts:
+            e.step(act[b:b + c].contiguous())
+    for b, c, e in parts:
+        assert torch.equal(e.obs_block, whole.obs_block[:, b:b + c])
+        assert torch.equal(e.scans, whole.scans[b:b + c])
+        assert torch.equal(e.episode_count, whole.episode_count[b:b + c]) and torch.equal(e.toggle_list, whole.toggle_list[b:b + c])
+    sc = whole.scans
+    assert bool(torch.isfinite(sc).all()) and bool(torch.isfinite(whole.obs_block).all())
+    assert float(sc.min()) > -0.1 and float(sc.max()) < 30.1             # [0, max_range] + N(0, 0.01) noise
+    assert bool((whole.lap_counts == (whole.toggle_list // 2).to(whole.lap_counts.dtype)).all())
+    assert int(whole.episode_count.max()) >= 2 and bool((whole.collisions == whole.in_collision.to(whole.collisions.dtype)).all())
