@@ -384,3 +384,40 @@ def test_full_size_config3_matches_small_batches_of_the_same_envs():
     assert float(sc.min()) > -0.1 and float(sc.max()) < 30.1             # [0, max_range] + N(0, 0.01) noise
     assert bool((whole.lap_counts == (whole.toggle_list // 2).to(whole.lap_counts.dtype)).all())
     assert int(whole.episode_count.max()) >= 2 and bool((whole.collisions == whole.in_collision.to(whole.collisions.dtype)).all())
+
+
+def test_full_size_config4_matches_small_batches_of_the_same_envs():
+    """BASELINE config 4 at its full size (65 536 two-agent envs, fp64 parity path: ordered launch, one warp per scan,
+    opponent kernel over 131 072 agents) against small handles over slices of the same envs (CTA-per-scan kernels)."""
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    import torch
+    N, T = 65536, 60
+    rng = np.random.default_rng(4)
+    lead = raceline_poses(N)
+    lat = rng.uniform(-0.3, 0.3, N)
+    chase = lead.copy()
+    chase[:, 0] += -1.5 * np.cos(lead[:, 2]) - lat * np.sin(lead[:, 2])
+    chase[:, 1] += -1.5 * np.sin(lead[:, 2]) + lat * np.cos(lead[:, 2])
+    poses = np.stack([lead, chase], axis=1)
+    kw = dict(num_agents=2, map=os.path.join(MAPS, "example_map"), dtype="fp64", noise="numpy", seed=12345)
+    whole = BatchF110Env(num_envs=N, **kw)
+    parts = [(b, c, BatchF110Env(num_envs=c, env_offset=b, **kw)) for b, c in ((0, 1024), (40_000, 500))]
+    whole.reset(poses)
+    for b, c, e in parts:
+        e.reset(poses[b:b + c])
+    g = torch.Generator(device="cuda").manual_seed(12)
+    for t in range(T):
+        act = torch.rand((N, 2, 2), generator=g, device="cuda", dtype=torch.float64)
+        act[..., 0] = (act[..., 0] * 2 - 1) * 0.2
+        act[:, 0, 1] = act[:, 0, 1] * 4.0
+        act[:, 1, 1] = 2.0 + act[:, 1, 1] * 6.0
+        whole.step(act)
+        for b, c, e in parts:
+            e.step(act[b:b + c].contiguous())
+    for b, c, e in parts:
+        assert torch.equal(e.obs_block, whole.obs_block[:, b:b + c])
+        assert torch.equal(e.scans, whole.scans[b:b + c])
+        assert torch.equal(e.collision_idx, whole.collision_idx[b:b + c]) and torch.equal(e.toggle_list, whole.toggle_list[b:b + c])
+    assert bool(torch.isfinite(whole.scans).all()) and bool((whole.collision_idx >= 0).any())      # GJK did fire somewhere
+    assert float(whole.scans.min()) > -0.1 and float(whole.scans.max()) < 30.1
