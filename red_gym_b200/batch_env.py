@@ -85,7 +85,7 @@ class BatchF110Env(object):
         if map_data is not None:
             self._upload_map(map_data)
         else:
-            self._upload_map(host.MapData(self.map_path, self.map_ext, edt=kwargs.get("edt", "scipy")))
+            self._upload_map(host.MapData(self.map_path, self.map_ext, edt=kwargs.get("edt", "gpu")))
         if self.noise == "numpy":
             self._ensure_noise(64)
         if reset_poses is not None:

@@ -38,9 +38,9 @@ def test_env_with_device_edt_matches_host_edt():
     poses = raceline_poses(500)
     kw = dict(num_envs=1, num_agents=1, map=os.path.join(MAPS, "example_map"), noise="off")
     for dtype in ("fp64", "fp32"):
-        a = BatchF110Env(dtype=dtype, **kw)
-        b = BatchF110Env(dtype=dtype, edt="gpu", **kw)
-        assert b.map.edt is None
+        a = BatchF110Env(dtype=dtype, edt="scipy", **kw)     # get_dt on the host, like the reference
+        b = BatchF110Env(dtype=dtype, **kw)                  # default: device EDT
+        assert b.map.edt is None and a.map.edt is not None
         assert (a.raycast(poses) == b.raycast(poses)).all()
         b.update_map(os.path.join(MAPS, "berlin.yaml"), ".png")            # default: device EDT
         a.update_map(os.path.join(MAPS, "berlin.yaml"), ".png", edt="scipy")
