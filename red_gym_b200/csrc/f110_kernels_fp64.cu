@@ -283,9 +283,11 @@ static __device__ __forceinline__ int theta_index_of(const F110Dev &d, const Sca
     return k;
 }
 
+// `writer`: this thread stores the row (lane 0 when a whole warp prepares one scan, every calling thread when
+// threads prepare one scan each).  The caller synchronises before the row is read.
 template <bool ROT, bool POW2, bool STEP>
 static __device__ __forceinline__ void scan_setup64(const F110Dev &d, double px, double py, double yaw, double vel,
-                                                    double *out, const double *noise_row, Scan64 *c)
+                                                    double *out, const double *noise_row, Scan64 *c, bool writer)
 {
     double xt = px - d.ox, yt = py - d.oy;
     double xr = ROT ? xt * d.oc + yt * d.os : xt;
@@ -295,7 +297,7 @@ static __device__ __forceinline__ void scan_setup64(const F110Dev &d, double px,
     float y_lo = margin - (float)yr, y_hi = (float)d.ymax - margin - (float)yr;
     double d0 = edt_lookup<ROT, POW2, true>(d, px, py);
     double t0 = theta_start(d, yaw);
-    if ((threadIdx.x & 31) == 0) {
+    if (writer) {
         c->x_lo = x_lo; c->x_hi = x_hi; c->y_lo = y_lo; c->y_hi = y_hi;
         c->max_fast = (x_lo <= 0.f && x_hi >= 0.f && y_lo <= 0.f && y_hi >= 0.f) ? (float)d.max_range : -1.0f;
         c->px = px; c->py = py; c->d0 = d0; c->t0 = t0; c->vel = vel;
@@ -303,7 +305,6 @@ static __device__ __forceinline__ void scan_setup64(const F110Dev &d, double px,
         c->r_gate = (STEP && vel != 0.0) ? (double)d.side_max32 * 1.0001 + 1.2 * d.ttc_thresh * fabs(vel) : -1.0;
         c->out = out; c->noise = noise_row;
     }
-    __syncwarp();
 }
 
 // trace_ray (laser_models.py:107-146) given the first lookup d0 at the scan origin
@@ -402,17 +403,12 @@ static __device__ __forceinline__ void scan_rounds_claimed(const F110Dev &d, con
 // per 262144 scans (example_map, power-of-two resolution): 64 regs 4.34 ms, 48 regs 4.08 ms, 40 regs 3.92 ms with the per-scan
 // constants in registers; with the shared-memory row 40 regs 3.37 ms, 32 regs (MINB = 8, no spill) 3.09 ms
 // SPLIT: one CTA (8 warps) per scan instead of one warp per scan
-template <bool ROT, bool POW2, bool COUNT, int MINB, bool SPLIT>
-__global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int env_begin, int env_count)
+// the env kernels' per-scan preparation: state -> Scan64 row
+template <bool ROT, bool POW2>
+static __device__ __forceinline__ void prepare_env_scan64(const F110Dev &d, int ia, Scan64 *c, bool writer)
 {
     const int NA = d.n_envs * d.n_agents;
-    int w = SPLIT ? f110_split_scan((int)blockIdx.x, env_count * d.n_agents, d.n_sm) : (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-    if (w >= env_count * d.n_agents) return;
-    int ia = env_begin * d.n_agents + w;
-    if (d.order) ia = d.order[ia];      // spatial launch order (f110_order.cu)
-    int e = ia / d.n_agents;
-    if (d.step_mask && !d.step_mask[e]) return;
-    const int lane = threadIdx.x & 31;
+    const int e = ia / d.n_agents;
     double px = d.state[ia], py = d.state[(size_t)NA + ia];
     double vel = d.state[3 * (size_t)NA + ia], yaw = d.state[4 * (size_t)NA + ia];
     const double *noise_row = nullptr;
@@ -421,13 +417,48 @@ __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int en
         if (row >= d.noise_rows) row %= d.noise_rows;
         noise_row = d.noise + row * d.n_beams;
     }
+    scan_setup64<ROT, POW2, true>(d, px, py, yaw, vel, (double *)d.scans + (size_t)ia * d.n_beams, noise_row, c, writer);
+}
+
+// One warp per scan (!SPLIT): threads 0..7 of the CTA prepare its 8 scans side by side (fp64 division, fmod and the
+// origin lookup: a few hundred instructions that 32 identical lanes per warp would otherwise repeat 8 times over).
+template <bool ROT, bool POW2, bool COUNT, int MINB, bool SPLIT>
+__global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int env_begin, int env_count)
+{
+    const int NA = d.n_envs * d.n_agents;
+    const int lane = threadIdx.x & 31;
+    __shared__ Scan64 rows[8];
+    __shared__ int row_ia[8];
+    __shared__ int next_round;
+    int ia;
+    Scan64 *c;
+    if (SPLIT) {
+        int w = f110_split_scan((int)blockIdx.x, env_count * d.n_agents, d.n_sm);
+        if (w >= env_count * d.n_agents) return;
+        ia = env_begin * d.n_agents + w;
+        if (d.order) ia = d.order[ia];      // spatial launch order (f110_order.cu)
+        if (d.step_mask && !d.step_mask[ia / d.n_agents]) return;
+        c = rows;
+        if (threadIdx.x < 32) prepare_env_scan64<ROT, POW2>(d, ia, c, lane == 0);
+    } else {
+        if (threadIdx.x < 8) {
+            const int w = (int)blockIdx.x * 8 + (int)threadIdx.x;
+            int a = -1;
+            if (w < env_count * d.n_agents) {
+                a = env_begin * d.n_agents + w;
+                if (d.order) a = d.order[a];
+                if (d.step_mask && !d.step_mask[a / d.n_agents]) a = -1;
+                else prepare_env_scan64<ROT, POW2>(d, a, rows + threadIdx.x, true);
+            }
+            row_ia[threadIdx.x] = a;
+        }
+        __syncthreads();
+        ia = row_ia[threadIdx.x >> 5];
+        if (ia < 0) return;
+        c = rows + (threadIdx.x >> 5);
+    }
     bool hit = false;
     unsigned nlook = 0;
-    __shared__ Scan64 rows[8];
-    Scan64 *c = rows + (SPLIT ? 0 : (threadIdx.x >> 5));
-    if (!SPLIT || threadIdx.x < 32)
-        scan_setup64<ROT, POW2, true>(d, px, py, yaw, vel, (double *)d.scans + (size_t)ia * d.n_beams, noise_row, c);
-    __shared__ int next_round;
     if (SPLIT) {
         if (threadIdx.x == 0) next_round = 0;
         __syncthreads();                        // one row for the CTA, written by its first warp
@@ -456,18 +487,36 @@ template <bool ROT, bool POW2, bool COUNT, bool SPLIT>
 __global__ void __launch_bounds__(256) k_scan_only64(const F110Dev d, const double *__restrict__ poses, int n,
                                                      double *__restrict__ out, const int *__restrict__ order)
 {
-    int w = SPLIT ? f110_split_scan((int)blockIdx.x, n, d.n_sm) : (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-    if (w >= n) return;
-    if (order) w = order[w];
+    __shared__ Scan64 rows[8];
+    __shared__ int row_ok[8];
+    __shared__ int next_round;
+    Scan64 *c;
+    if (SPLIT) {
+        int w = f110_split_scan((int)blockIdx.x, n, d.n_sm);
+        if (w >= n) return;
+        if (order) w = order[w];
+        c = rows;
+        if (threadIdx.x < 32)
+            scan_setup64<ROT, POW2, false>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], 0.0, out + (size_t)w * d.n_beams, nullptr, c,
+                                           threadIdx.x == 0);
+        if (threadIdx.x == 0) next_round = 0;
+        __syncthreads();
+    } else {
+        if (threadIdx.x < 8) {
+            int w = (int)blockIdx.x * 8 + (int)threadIdx.x;
+            row_ok[threadIdx.x] = w < n;
+            if (w < n) {
+                if (order) w = order[w];
+                scan_setup64<ROT, POW2, false>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], 0.0, out + (size_t)w * d.n_beams, nullptr,
+                                               rows + threadIdx.x, true);
+            }
+        }
+        __syncthreads();
+        if (!row_ok[threadIdx.x >> 5]) return;
+        c = rows + (threadIdx.x >> 5);
+    }
     bool hit = false;
     unsigned nlook = 0;
-    __shared__ Scan64 rows[8];
-    Scan64 *c = rows + (SPLIT ? 0 : (threadIdx.x >> 5));
-    if (!SPLIT || threadIdx.x < 32)
-        scan_setup64<ROT, POW2, false>(d, poses[3 * w], poses[3 * w + 1], poses[3 * w + 2], 0.0, out + (size_t)w * d.n_beams, nullptr, c);
-    __shared__ int next_round;
-    if (SPLIT && threadIdx.x == 0) next_round = 0;
-    if (SPLIT) __syncthreads();
     if (SPLIT) scan_rounds_claimed<ROT, POW2, false, COUNT>(d, c, hit, nlook, &next_round);
     else scan_rounds<ROT, POW2, false, COUNT>(d, c, hit, nlook);
     if (COUNT) {
