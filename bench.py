@@ -473,6 +473,7 @@ def cpu_reference(workload, seconds=12.0, nthreads=0):
             env.reset(poses, mask=d)
     dt = time.perf_counter() - t0
     return {"value": n * agents * steps / dt, "unit": "agent-steps/s", "cores": nthreads or cores, "kind": "port",
+            "sample_envs": n, "sample_ms_per_step": 1e3 * dt / max(steps, 1),
             "sample": "%d envs x %d steps (%.1f s) of %s on example_map, fp64, numpy noise rows, host auto-reset" % (n, steps, dt, workload)}
 
 
@@ -485,9 +486,12 @@ def run_reference(args):
     cb = cpu_reference(args.workload, seconds=seconds)
     n_envs, agents, dtype, noise, auto = WORKLOADS[args.workload]
     line = {"impl": "reference", "metric": "agent-steps/sec (1080-beam lidar)", "value": cb["value"], "unit": "agent-steps/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["sample_ms_per_step"],
+            "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": args.workload, "agents": agents, "beams": 1080, "map": "example_map", "integrator": "RK4"},
+            "config": {"workload": args.workload, "envs_per_step": cb["sample_envs"], "agents": agents, "beams": 1080, "map": "example_map",
+                       "integrator": "RK4", "noise": "numpy", "auto_reset": True,
+                       "note": "a step of this arm = one step of the bounded sample of the workload (64 envs per host thread)"},
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))

@@ -1,10 +1,10 @@
 #!/bin/bash
-# Batch-size sweep of the step (config 3 workload): units (default) vs one warp per scan (variant 256), both dtypes.
-# usage: tools/batch_sweep.sh out.jsonl [sizes...]
+# Batch-size sweep of the step (config 3 workload) over raycast variants (default: 0), both dtypes.
+# usage: VARIANTS="0 128" tools/batch_sweep.sh out.jsonl [sizes...]
 out=$1; shift
 sizes=${@:-"4096 8192 16384 32768 65536 131072"}
 : > $out
-for dt in fp32 fp64; do for n in $sizes; do for v in 0 256; do
+for dt in fp32 fp64; do for n in $sizes; do for v in ${VARIANTS:-0}; do
   line=$(timeout 120 python bench.py --envs $n --dtype $dt --variant $v --no-cpu --no-e2e --steps 40 --warmup 10 2>/dev/null | grep '^{' | tail -1)
   echo "{\"dtype\": \"$dt\", \"envs\": $n, \"variant\": $v, \"line\": $line}" >> $out
   python - "$line" $dt $n $v <<'PY'
