@@ -93,7 +93,9 @@ def gen_scans(map_name, fov_name, beams=1080, n_poses=20):
 
 # ----------------------------------------------------------------------------- rollouts
 def _rollout(tag, map_name, num_agents, integrator_name, fov_name, n_envs, n_steps, poses0, actions,
-             scan_every, seed=12345, params=None):
+             scan_every, seed=12345, params=None, timestep=0.01, ego_idx=0, agent_params=None):
+    """agent_params: {agent index: params dict} applied through F110Env.update_params(params, index) after
+    construction (base_classes.py:507-527)."""
     gym = _ref()
     from f110_gym.envs.base_classes import Integrator
     integ = getattr(Integrator, integrator_name)
@@ -111,11 +113,14 @@ def _rollout(tag, map_name, num_agents, integrator_name, fov_name, n_envs, n_ste
     scans = np.zeros((n_envs, scan_steps.size, A, 1080))
     scan_sum = np.zeros((n_envs, n_steps + 1, A))
     scan_min = np.zeros((n_envs, n_steps + 1, A))
-    kw = dict(map=MAPS[map_name], map_ext=".png", num_agents=A, timestep=0.01, integrator=integ, fov=fov, seed=seed)
+    kw = dict(map=MAPS[map_name], map_ext=".png", num_agents=A, timestep=timestep, integrator=integ, fov=fov, seed=seed,
+              ego_idx=ego_idx)
     if params is not None:
         kw["params"] = params
     for e in range(n_envs):
         env = gym.make("f110_gym:f110-v0", **kw)
+        for a, p_a in (agent_params or {}).items():
+            env.update_params(p_a, index=a)
 
         def rec(t, obs, d):
             for a in range(A):
@@ -141,8 +146,13 @@ def _rollout(tag, map_name, num_agents, integrator_name, fov_name, n_envs, n_ste
             obs, r, d, info = env.step(actions[t, e].copy())
             rec(t + 1, obs, d)
     out = os.path.join(GOLDEN, tag + ".npz")
+    extra = {}
+    if agent_params:
+        keys = sorted(next(iter(agent_params.values())).keys())
+        extra = dict(agent_param_idx=np.array(sorted(agent_params)), agent_param_keys=np.array(keys),
+                     agent_param_vals=np.array([[agent_params[a][k] for k in keys] for a in sorted(agent_params)]))
     np.savez_compressed(out, map=map_name, num_agents=A, integrator=integrator_name, fov=fov, seed=seed,
-                        poses0=poses0, actions=actions, states=S, obs_pose=obs_pose, collisions=coll,
+                        timestep=timestep, ego_idx=ego_idx, **extra, poses0=poses0, actions=actions, states=S, obs_pose=obs_pose, collisions=coll,
                         collision_idx=cidx, toggles=tog, lap_counts=lapc, lap_times=lapt, done=done,
                         scan_steps=scan_steps, scans=scans, scan_sum=scan_sum, scan_min=scan_min)
     print("wrote", out, "collided envs:", int((coll.max(axis=(1, 2)) > 0).sum()), "of", n_envs,
@@ -215,6 +225,31 @@ def gen_rollout_a3():
     act[..., 0] = rng.uniform(-0.2, 0.2, (T // 15 + 1, n, 3)).repeat(15, axis=0)[:T]
     act[..., 1] = rng.uniform(0.5, 4.0, (T // 15 + 1, n, 3)).repeat(15, axis=0)[:T]
     _rollout("rollout_a3_skirk", "skirk", 3, "RK4", "2pi", n, T, poses0, act, 100, seed=31)
+
+
+def gen_rollout_a2_ego1():
+    # the knobs the other rollouts leave at their defaults: ego_idx = 1 (done follows agent 1's collision flag and the
+    # lap frame is agent 1's start pose, f110_env.py:292-299, 318-323), timestep 0.02, a heavier / shorter car for agent 0
+    # set through update_params(index=0) (its own side_distances are NOT rebuilt by the reference: base_classes.py:116-156
+    # runs once per process), vegas map
+    n, T = 6, 400
+    rng = np.random.default_rng(21)
+    base = np.array([[0.0, 0.0, 0.0], [0.1, -0.1, 0.3], [-0.2, 0.1, -0.4], [0.0, 0.2, 3.0], [0.3, 0.0, 1.6], [-0.1, -0.2, 4.6]])
+    poses0 = np.zeros((n, 2, 3))
+    for e in range(n):
+        th = base[e, 2]
+        poses0[e, 0] = base[e]
+        lat = rng.uniform(-0.25, 0.25)
+        poses0[e, 1] = [base[e, 0] - 1.2 * np.cos(th) - lat * np.sin(th), base[e, 1] - 1.2 * np.sin(th) + lat * np.cos(th), th + 0.05]
+    act = np.zeros((T, n, 2, 2))
+    act[..., 0] = rng.uniform(-0.2, 0.2, (T // 10 + 1, n, 2)).repeat(10, axis=0)[:T]
+    act[:, :, 0, 1] = rng.uniform(0.0, 3.0, (T // 10 + 1, n)).repeat(10, axis=0)[:T]
+    act[:, :, 1, 1] = rng.uniform(1.0, 7.0, (T // 10 + 1, n)).repeat(10, axis=0)[:T]
+    p0 = {'mu': 0.9, 'C_Sf': 4.2, 'C_Sr': 5.0, 'lf': 0.14, 'lr': 0.16, 'h': 0.08, 'm': 4.5, 'I': 0.05,
+          's_min': -0.35, 's_max': 0.35, 'sv_min': -2.5, 'sv_max': 2.5, 'v_switch': 6.0, 'a_max': 7.0,
+          'v_min': -4.0, 'v_max': 15.0, 'width': 0.28, 'length': 0.5}
+    _rollout("rollout_a2_ego1_dt02_vegas", "vegas", 2, "RK4", "2pi", n, T, poses0, act, 100, seed=99,
+             timestep=0.02, ego_idx=1, agent_params={0: p0})
 
 
 def gen_waypoint_follow():
@@ -309,6 +344,7 @@ SCENARIOS = {
     "rollout_a1_euler": gen_rollout_a1_euler,
     "rollout_a2": gen_rollout_a2,
     "rollout_a3": gen_rollout_a3,
+    "rollout_a2_ego1": gen_rollout_a2_ego1,
     "waypoint_follow": gen_waypoint_follow,
 }
 for _m in MAPS:

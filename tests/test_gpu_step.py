@@ -29,10 +29,15 @@ def test_rollouts_match_reference_goldens(path):
     d = np.load(path)
     A = int(d["num_agents"])
     N, T = d["poses0"].shape[0], d["actions"].shape[0]
+    dt = float(d["timestep"]) if "timestep" in d.files else 0.01
     env = BatchF110Env(num_envs=N, num_agents=A, map=os.path.join(MAPS, str(d["map"])), fov=float(d["fov"]),
-                       integrator=str(d["integrator"]), seed=int(d["seed"]))
+                       integrator=str(d["integrator"]), seed=int(d["seed"]), timestep=dt,
+                       ego_idx=int(d["ego_idx"]) if "ego_idx" in d.files else 0)
+    if "agent_param_idx" in d.files:        # F110Env.update_params(params, index) after construction
+        for a, vals in zip(d["agent_param_idx"], d["agent_param_vals"]):
+            env.update_params(dict(zip([str(k) for k in d["agent_param_keys"]], vals)), index=int(a))
     obs, rew, done, info = env.reset(d["poses0"])
-    assert rew == 0.01
+    assert rew == dt
     steps = list(d["scan_steps"])
     for t in range(T + 1):
         if t > 0:
