@@ -199,7 +199,7 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
     }
     d.actions = s->actions;
     // spatial launch order: pays once more scans are in flight than the GPU holds at a time (and costs 3 small launches)
-    s->use_order = NA >= 32768 && !(cfg->raycast_variant & 64);
+    s->use_order = NA >= F110_ORDER_FROM && !(cfg->raycast_variant & 64);
     if (s->use_order) {
         if (dev_alloc(s, &s->order_buf, 3 * NA)) { f110_destroy(s); return F110_ERR_NOMEM; }
         d.order_chunk_envs = (A == 1 && N >= 8192) ? (int)((N + 7) / 8) : (int)N;   // same chunks as f110_step_host
@@ -675,7 +675,7 @@ extern "C" int f110_raycast(f110_sim *s, const double *poses_dev, int32_t n, voi
     if (!poses_dev || !out_dev || n < 0) return fail(F110_ERR_INVALID, "bad raycast arguments");
     CK(cudaSetDevice(s->device));
     const int *order = nullptr;
-    if (n >= 32768 && !(s->cfg.raycast_variant & 64)) {    // same reasoning as in the step: neighbours in launch order = neighbours on the map
+    if (n >= F110_ORDER_FROM && !(s->cfg.raycast_variant & 64)) {    // same reasoning as in the step: neighbours in launch order = neighbours on the map
         if ((size_t)n > s->rc_order_cap) {
             CK(cudaStreamSynchronize((cudaStream_t)stream));
             if (s->rc_order_buf) cudaFree(s->rc_order_buf);

@@ -19,6 +19,10 @@ enum { F110_P_MU, F110_P_CSF, F110_P_CSR, F110_P_LF, F110_P_LR, F110_P_H, F110_P
 // slowest of the 8 warps, ncu stall_barrier 18.8, not the L1 hit rate).  The grid is n_sm * ceil(n / n_sm) CTAs; the surplus ones exit.
 static __host__ __device__ __forceinline__ int f110_split_grid(int n, int n_sm) { return n_sm * ((n + n_sm - 1) / n_sm); }
 static __device__ __forceinline__ int f110_split_scan(int b, int n, int n_sm) { return (b % n_sm) * ((n + n_sm - 1) / n_sm) + b / n_sm; }
+// Launches of at least this many scans are put in spatial order first (f110_order.cu: three small kernels, ~25 us with
+// their launch gaps).  At 16384 scans that costs what it saves (measured: ray-cast 0.189 -> 0.181 ms, step 0.179 -> 0.200 ms
+// 50 steps after a reset, about break-even once env order has fully decorrelated from track order).
+#define F110_ORDER_FROM 32768
 #define F110_SPLIT_BELOW64 6144
 #define F110_SPLIT_BELOW32 3072
 
