@@ -173,7 +173,9 @@ int f110_step(f110_sim *sim, const double *actions_dev, void *stream);
  * copies actions in, steps, copies the observation out, and returns when the host buffers are
  * valid.  obs_block_host: [10][N*A] doubles (see f110_buffers.obs_block) or NULL;
  * scans_host: [N][A][B] in the handle's scan type or NULL; done_host: [N] bytes or NULL.
- * Page-locked host buffers give full PCIe rate; pageable ones work. */
+ * Page-locked host buffers give full PCIe rate; pageable ones work.  When all of them are page-locked AND mapped
+ * (cudaHostAlloc / torch pin_memory) and the observation is below 256 KB (a handful of envs), the step reads the
+ * actions and writes the observation directly over PCIe from its kernels instead of using the copy engines. */
 int f110_step_host(f110_sim *sim, const double *actions_host, double *obs_block_host, void *scans_host,
                    uint8_t *done_host, void *stream);
 

@@ -613,6 +613,30 @@ extern "C" int f110_step(f110_sim *s, const double *actions_dev, void *stream)
     return rc;
 }
 
+// Small batches through f110_step_host: the observation is a few KB and three cudaMemcpyAsync + their engine switches
+// cost more than the kernels.  When every host buffer is page-locked and mapped (what cudaHostAlloc / torch pin_memory
+// give under unified addressing), the step reads the actions straight from the host buffer and one more kernel writes
+// obs_block, scans and done straight into the host buffers (posted PCIe writes): no copy engine involved.  Same bytes.
+__global__ void __launch_bounds__(256) k_export_host(const double *__restrict__ obs, double *__restrict__ obs_h, size_t n_obs,
+                                                     const unsigned *__restrict__ scans, unsigned *__restrict__ scans_h, size_t n_scan_words,
+                                                     const uint8_t *__restrict__ done, uint8_t *__restrict__ done_h, size_t n_done)
+{
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nt = (size_t)gridDim.x * blockDim.x;
+    if (obs_h) for (size_t i = t; i < n_obs; i += nt) obs_h[i] = obs[i];
+    if (scans_h) for (size_t i = t; i < n_scan_words; i += nt) scans_h[i] = scans[i];
+    if (done_h) for (size_t i = t; i < n_done; i += nt) done_h[i] = done[i];
+}
+
+// device-side address of a page-locked, mapped host buffer; null if p is anything else (pageable, device, null)
+static void *mapped_host_ptr(const void *p)
+{
+    if (!p) return nullptr;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
+}
+#define F110_ZERO_COPY_MAX_BYTES (256 * 1024)
+
 extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *obs_block_host, void *scans_host,
                               uint8_t *done_host, void *stream)
 {
@@ -623,6 +647,26 @@ extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *o
     F110Dev &d = s->d;
     const size_t N = d.n_envs, A = d.n_agents, NA = N * A, B = d.n_beams;
     const size_t esz = d.scan_is_f32 ? 4 : 8;
+    if ((scans_host ? NA * B * esz : 0) + 10 * NA * 8 <= F110_ZERO_COPY_MAX_BYTES) {
+        const double *act_d = (const double *)mapped_host_ptr(actions_host);
+        double *obs_d = (double *)mapped_host_ptr(obs_block_host);
+        unsigned *scans_d = (unsigned *)mapped_host_ptr(scans_host);
+        uint8_t *done_d = (uint8_t *)mapped_host_ptr(done_host);
+        if (act_d && (obs_d || !obs_block_host) && (scans_d || !scans_host) && (done_d || !done_host)) {
+            s->d.actions = act_d;
+            int rc = enqueue_step(s, nullptr, st);
+            s->d.actions = s->actions;
+            if (rc) return rc;
+            const size_t words = NA * B * (esz / 4);
+            const int grid = (int)((words / 4 + 255) / 256);
+            k_export_host<<<grid < 1 ? 1 : (grid > 64 ? 64 : grid), 256, 0, st>>>(s->obs_block, obs_d, 10 * NA, (const unsigned *)d.scans, scans_d,
+                                                                                    words, d.done, done_d, N);
+            s->launches++;
+            CK(cudaGetLastError());
+            CK(cudaStreamSynchronize(st));
+            return F110_OK;
+        }
+    }
     CK(cudaMemcpyAsync(s->actions, actions_host, 2 * NA * 8, cudaMemcpyHostToDevice, st));
     d.actions = s->actions;
     d.step_mask = nullptr;
