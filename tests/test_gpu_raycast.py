@@ -177,3 +177,54 @@ def test_fp32_sentinel_and_cap_scale_with_the_map(size, res):
     want = fo.OracleEnv(1, 1, map_data=md, noise=False).scan(poses)
     d = np.abs(got - want)
     assert np.median(d) < 1e-3 and (d > 2e-2).mean() < 0.03, (np.median(d), (d > 2e-2).mean(), d.max())
+
+
+@pytest.mark.gpu
+def test_fp32_philox_noise_is_gaussian_and_independent():
+    """The fp32 path replaces the reference's numpy stream (laser_models.py:448-452: rng.normal(0, std_dev, B)) by a
+    counter-based Philox4x32-10 + Box-Muller stream.  Validated on its own: cars at rest (zero action: the pose does not
+    change, vel == 0 switches iTTC off), so noisy scan - noise-free scan is the noise alone."""
+    import torch
+    from scipy import stats
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    N, T, B = 512, 6, 1080
+    kw = dict(num_envs=N, num_agents=1, map=os.path.join(MAPS, "example_map"), dtype="fp32")
+    poses = raceline_poses(N)[:, None, :]
+    clean = BatchF110Env(noise="off", **kw)
+    clean.reset(poses)
+    base = clean.scans.clone()
+    noisy = BatchF110Env(noise="philox", seed=12345, **kw)
+    noisy.reset(poses)
+    first_scans = noisy.scans.clone()
+    zero = torch.zeros((N, 1, 2), dtype=torch.float64, device="cuda")
+    z = []
+    for t in range(T):
+        z.append(((noisy.scans - base).double() / 0.01).cpu().numpy()[:, 0, :])      # in units of sigma
+        noisy.step(zero)
+    z = np.stack(z)                                   # (T, N, B)
+    n = z.size
+    assert abs(z.mean()) < 5.0 / np.sqrt(n)
+    assert abs(z.std() - 1.0) < 5.0 / np.sqrt(2 * n) + 2e-4      # + fp32 rounding of range + noise at 30 m
+    assert abs(stats.skew(z.ravel())) < 5.0 * np.sqrt(6.0 / n)
+    assert abs(stats.kurtosis(z.ravel())) < 5.0 * np.sqrt(24.0 / n) + 2e-3
+    assert np.abs(z).max() < 4.9 and np.abs(z).max() > 4.0         # 16-bit uniforms: radius truncated at 4.85 sigma
+    assert stats.kstest(z[0].ravel()[:200000], "norm").pvalue > 1e-4
+    # independence: neighbouring beams, the same beam in neighbouring envs and in consecutive steps, the two halves of a Box-Muller pair
+    lim = 5.0 / np.sqrt(n)
+    def corr(a, b):
+        return float((a * b).mean())
+    assert abs(corr(z[:, :, :-1], z[:, :, 1:])) < lim
+    assert abs(corr(z[:, :, :-32], z[:, :, 32:])) < lim          # next round of the same lane: other half of its Box-Muller pair
+    assert abs(corr(z[:, :, :-64], z[:, :, 64:])) < lim
+    assert abs(corr(z[:, :-1], z[:, 1:])) < lim
+    assert abs(corr(z[:-1], z[1:])) < lim
+    # per-beam and per-env variances are all alike (no beam / env with a degenerate stream)
+    assert np.abs(z.std(axis=(0, 1)) - 1.0).max() < 0.1 and np.abs(z.std(axis=(0, 2)) - 1.0).max() < 0.1
+    # same seed -> same stream (reference ScanTests.test_rng); another seed -> another stream
+    again = BatchF110Env(noise="philox", seed=12345, **kw)
+    again.reset(poses)
+    other = BatchF110Env(noise="philox", seed=777, **kw)
+    other.reset(poses)
+    assert torch.equal(again.scans, first_scans)
+    assert not torch.allclose(other.scans, first_scans, atol=1e-4)
