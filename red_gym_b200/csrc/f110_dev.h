@@ -8,23 +8,32 @@ enum { F110_P_MU, F110_P_CSF, F110_P_CSR, F110_P_LF, F110_P_LR, F110_P_H, F110_P
        F110_P_SMAX, F110_P_SVMIN, F110_P_SVMAX, F110_P_VSWITCH, F110_P_AMAX, F110_P_VMIN, F110_P_VMAX,
        F110_P_WIDTH, F110_P_LENGTH, F110_NP };
 
-// Launches of fewer scans than this give each scan a CTA of 8 warps instead of one warp (k_*split / SPLIT = true):
-// one warp per scan would leave most of the GPU waiting on ~365 dependent gathers in a row.  The warps of the CTA
-// claim rounds of 32 beams from a shared counter.  Measured per step, split / one warp per scan: fp64 256 envs
-// 0.069 / 0.138 ms, 2048 envs 0.090 / 0.12, 4096 envs 0.129 / 0.173, 8192 envs 0.22 / 0.196; fp32 256 envs
-// 0.053 / 0.095, 2048 envs 0.082 / 0.10, 4096 envs 0.127 / 0.123, 8192 envs 0.193 / 0.139.  Variant bit 7 turns it off.
-// Split launches map CTA b to scan (b % n_sm) * ceil(n / n_sm) + b / n_sm: CTAs are handed to the SMs round-robin,
+// Launches of fewer scans than F110_SPLIT_BELOW* share a scan between the warps of a CTA (k_*split / SPLIT = true) instead of
+// giving it one warp: one warp per scan would leave most of the GPU waiting on ~365 dependent gathers in a row.  The warps
+// claim rounds of 32 beams from a shared counter.  A scan gets 8, 4 or 2 warps (f110_split_wps: the most that still make about
+// one wave of CTAs); the CTA holds 8 / that many scans.  Measured per step, split / one warp per scan: fp64 1184 envs
+// 0.082 / 0.148 ms, 2368: 0.085 / 0.160, 4096: 0.121 / 0.172, 8192: 0.168 / 0.189, 16384: 0.280 / 0.292, 24576: 0.384 / 0.387;
+// fp32 1184 envs 0.068 / 0.104, 2368: 0.084 / 0.113, 3072: 0.095 / 0.115, 4096: 0.115 / 0.119, 5120: 0.125 / 0.122.
+// (With 8 warps per scan at every size: fp64 4096 envs 0.127, fp32 worse than one warp per scan from 4096 on.)
+// Variant bit 7 turns the split off, bit 11 keeps 8 warps per scan, bit 12 splits at any size.
+// Split launches map CTA b to group (b % n_sm) * ceil(n / n_sm) + b / n_sm: CTAs are handed to the SMs round-robin,
 // so the CTAs resident on one SM then hold consecutive scans (neighbours on the track, overlapping EDT footprints)
-// instead of scans n_sm apart (worth 2 % at 4096 scans: what holds the split kernels back is the CTA-wide wait for the
-// slowest of the 8 warps, ncu stall_barrier 18.8, not the L1 hit rate).  The grid is n_sm * ceil(n / n_sm) CTAs; the surplus ones exit.
+// instead of scans n_sm apart.  The grid is n_sm * ceil(n / n_sm) CTAs; the surplus ones exit.
 static __host__ __device__ __forceinline__ int f110_split_grid(int n, int n_sm) { return n_sm * ((n + n_sm - 1) / n_sm); }
 static __device__ __forceinline__ int f110_split_scan(int b, int n, int n_sm) { return (b % n_sm) * ((n + n_sm - 1) / n_sm) + b / n_sm; }
 // Launches of at least this many scans are put in spatial order first (f110_order.cu: three small kernels, ~25 us with
 // their launch gaps).  At 16384 scans that costs what it saves (measured: ray-cast 0.189 -> 0.181 ms, step 0.179 -> 0.200 ms
 // 50 steps after a reset, about break-even once env order has fully decorrelated from track order).
 #define F110_ORDER_FROM 32768
-#define F110_SPLIT_BELOW64 6144
-#define F110_SPLIT_BELOW32 3072
+// warps per scan of a split launch of n scans: 8, 4 or 2, the largest that still makes about one wave of CTAs
+// (8 CTAs of 8 warps per SM), see k_raycast64
+static __host__ __device__ __forceinline__ int f110_split_wps(int n, int n_sm)
+{
+    const long long slots = 64LL * n_sm;          // warps in flight
+    return (long long)n * 8 <= slots ? 8 : (long long)n * 4 <= slots ? 4 : 2;
+}
+#define F110_SPLIT_BELOW64 20480
+#define F110_SPLIT_BELOW32 4608
 
 struct F110Dev {
     int n_envs, n_agents, n_beams, integrator, ego_idx, theta_dis;

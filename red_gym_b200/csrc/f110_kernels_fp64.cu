@@ -385,10 +385,11 @@ static __device__ __forceinline__ void scan_rounds(const F110Dev &d, const Scan6
 
 // the CTA-per-scan version: warps claim rounds from `next`
 template <bool ROT, bool POW2, bool STEP, bool COUNT>
-static __device__ __forceinline__ void scan_rounds_claimed(const F110Dev &d, const Scan64 *c, bool &hit_any, unsigned &nlook, int *next)
+static __device__ __forceinline__ void scan_rounds_claimed(const F110Dev &d, const Scan64 *c, bool &hit_any, unsigned &nlook, int *next,
+                                                           bool counts_origin = (threadIdx.x == 0))
 {
     const int lane = threadIdx.x & 31;
-    if (COUNT) nlook += (threadIdx.x == 0);
+    if (COUNT) nlook += counts_origin;
     const int rounds = (d.n_beams + 31) >> 5;
     for (;;) {
         int r = 0;
@@ -422,54 +423,57 @@ static __device__ __forceinline__ void prepare_env_scan64(const F110Dev &d, int 
 
 // One warp per scan (!SPLIT): threads 0..7 of the CTA prepare its 8 scans side by side (fp64 division, fmod and the
 // origin lookup: a few hundred instructions that 32 identical lanes per warp would otherwise repeat 8 times over).
+// SPLIT: a scan is shared by `wps` warps (8, 4 or 2: the CTA holds 8 / wps scans) that claim its rounds one at a time.
+// Small launches pick wps so that the launch is about one wave of CTAs (f110_split_wps): with fewer, longer-lived
+// warps per scan more scans are in flight per SM at a time -- neighbours on the track, whose rays walk the same EDT
+// lines (ncu at 4096 scans, 8 warps per scan: L1 hit rate 52 % against 92 % in large launches) -- and no CTA of a last,
+// partly filled wave is left running alone.  The arithmetic per beam does not depend on wps.
 template <bool ROT, bool POW2, bool COUNT, int MINB, bool SPLIT>
-__global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int env_begin, int env_count)
+__global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int env_begin, int env_count, int wps)
 {
     const int NA = d.n_envs * d.n_agents;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     __shared__ Scan64 rows[8];
     __shared__ int row_ia[8];
-    __shared__ int next_round;
-    int ia;
-    Scan64 *c;
-    if (SPLIT) {
-        int w = f110_split_scan((int)blockIdx.x, env_count * d.n_agents, d.n_sm);
-        if (w >= env_count * d.n_agents) return;
-        ia = env_begin * d.n_agents + w;
-        if (d.order) ia = d.order[ia];      // spatial launch order (f110_order.cu)
-        if (d.step_mask && !d.step_mask[ia / d.n_agents]) return;
-        c = rows;
-        if (threadIdx.x < 32) prepare_env_scan64<ROT, POW2>(d, ia, c, lane == 0);
-    } else {
-        if (threadIdx.x < 8) {
-            const int w = (int)blockIdx.x * 8 + (int)threadIdx.x;
-            int a = -1;
-            if (w < env_count * d.n_agents) {
-                a = env_begin * d.n_agents + w;
-                if (d.order) a = d.order[a];
-                if (d.step_mask && !d.step_mask[a / d.n_agents]) a = -1;
-                else prepare_env_scan64<ROT, POW2>(d, a, rows + threadIdx.x, true);
-            }
-            row_ia[threadIdx.x] = a;
+    __shared__ int next_round[8], hit_any[8];
+    const int per_cta = SPLIT ? 8 / wps : 8;                  // scans of this CTA
+    const int slot = SPLIT ? warp / wps : warp;
+    if (threadIdx.x < per_cta) {
+        const int total = env_count * d.n_agents;
+        int cta = (int)blockIdx.x;
+        if (SPLIT) cta = f110_split_scan(cta, (total + per_cta - 1) / per_cta, d.n_sm);
+        const int w = cta * per_cta + (int)threadIdx.x;
+        int a = -1;
+        if (w < total && (!SPLIT || cta < (total + per_cta - 1) / per_cta)) {
+            a = env_begin * d.n_agents + w;
+            if (d.order) a = d.order[a];      // spatial launch order (f110_order.cu)
+            if (d.step_mask && !d.step_mask[a / d.n_agents]) a = -1;
+            else prepare_env_scan64<ROT, POW2>(d, a, rows + threadIdx.x, true);
         }
-        __syncthreads();
-        ia = row_ia[threadIdx.x >> 5];
-        if (ia < 0) return;
-        c = rows + (threadIdx.x >> 5);
+        row_ia[threadIdx.x] = a;
+        next_round[threadIdx.x] = 0;
+        hit_any[threadIdx.x] = 0;
     }
+    __syncthreads();
+    const int ia = row_ia[slot];
+    Scan64 *c = rows + slot;
     bool hit = false;
     unsigned nlook = 0;
     if (SPLIT) {
-        if (threadIdx.x == 0) next_round = 0;
-        __syncthreads();                        // one row for the CTA, written by its first warp
-        scan_rounds_claimed<ROT, POW2, true, COUNT>(d, c, hit, nlook, &next_round);
-        hit = __syncthreads_or(hit) != 0;       // every warp has read the state by now (the returns above are per CTA)
+        if (ia >= 0) {
+            scan_rounds_claimed<ROT, POW2, true, COUNT>(d, c, hit, nlook, &next_round[slot], lane == 0 && warp % wps == 0);
+            if (__any_sync(FULL, hit) && lane == 0) atomicOr(&hit_any[slot], 1);
+        }
+        __syncthreads();                        // every warp has read the state by now
+        hit = hit_any[slot] != 0;
+        if (ia < 0) return;
     } else {
+        if (ia < 0) return;
         scan_rounds<ROT, POW2, true, COUNT>(d, c, hit, nlook);
         hit = __any_sync(FULL, hit);
     }
     // RaceCar.check_ttc (base_classes.py:241-250): state[3:] = 0 -- velocity, YAW, yaw rate, slip
-    if (lane == 0 && (!SPLIT || threadIdx.x == 0)) {
+    if (lane == 0 && (!SPLIT || warp % wps == 0)) {
         if (hit) {
             d.state[3 * (size_t)NA + ia] = 0.; d.state[4 * (size_t)NA + ia] = 0.;
             d.state[5 * (size_t)NA + ia] = 0.; d.state[6 * (size_t)NA + ia] = 0.;
@@ -546,17 +550,18 @@ void f110_launch_raycast64(const F110Dev &d, int env_begin, int env_count, int v
 {
     long long warps = (long long)env_count * d.n_agents;
     if (warps == 0) return;
-    const bool split = warps < F110_SPLIT_BELOW64 && !(variant & 128);
-    int grid = split ? f110_split_grid((int)warps, d.n_sm) : (int)((warps * 32 + 255) / 256);
+    const bool split = (warps < F110_SPLIT_BELOW64 || (variant & 4096)) && !(variant & 128);     // bit 12: split at any size
+    const int wps = (variant & 2048) ? 8 : f110_split_wps((int)warps, d.n_sm);      // variant bit 11: always a CTA per scan
+    int grid = split ? f110_split_grid((int)((warps * wps + 7) / 8), d.n_sm) : (int)((warps * 32 + 255) / 256);
     const bool cnt = d.count_lookups != 0;
 #define RC64(R, P, MB, ALT)                                                                                         \
     do {                                                                                                          \
         if (split) {                                                                                              \
-            if (cnt) k_raycast64<R, P, true, 1, true><<<grid, 256, 0, st>>>(d, env_begin, env_count);             \
-            else k_raycast64<R, P, false, MB, true><<<grid, 256, 0, st>>>(d, env_begin, env_count);               \
-        } else if (cnt) k_raycast64<R, P, true, 1, false><<<grid, 256, 0, st>>>(d, env_begin, env_count);         \
-        else if (variant & 8) k_raycast64<R, P, false, ALT, false><<<grid, 256, 0, st>>>(d, env_begin, env_count); \
-        else k_raycast64<R, P, false, MB, false><<<grid, 256, 0, st>>>(d, env_begin, env_count);                  \
+            if (cnt) k_raycast64<R, P, true, 1, true><<<grid, 256, 0, st>>>(d, env_begin, env_count, wps);             \
+            else k_raycast64<R, P, false, MB, true><<<grid, 256, 0, st>>>(d, env_begin, env_count, wps);               \
+        } else if (cnt) k_raycast64<R, P, true, 1, false><<<grid, 256, 0, st>>>(d, env_begin, env_count, 1);         \
+        else if (variant & 8) k_raycast64<R, P, false, ALT, false><<<grid, 256, 0, st>>>(d, env_begin, env_count, 1); \
+        else k_raycast64<R, P, false, MB, false><<<grid, 256, 0, st>>>(d, env_begin, env_count, 1);                  \
     } while (0)
     // registers per thread: 32 (8 CTAs per SM) where the kernel fits without spilling, else 40; variant bit 3 swaps the two
     if (d.has_rot) RC64(true, false, 6, 8);

@@ -314,15 +314,16 @@ def test_spatial_launch_order_does_not_change_results(dtype, agents):
     assert (a_env.episode_count == b_env.episode_count).all()
 
 
-@pytest.mark.parametrize("dtype,agents", [("fp32", 1), ("fp64", 1), ("fp64", 2), ("fp32", 2)])
-def test_small_batch_split_scans_do_not_change_results(dtype, agents):
-    """Below 12288 scans a CTA of 8 warps shares one scan (F110_SPLIT_BELOW); raycast_variant=128 keeps one warp per
-    scan.  Same arithmetic per beam, so states, flags and scans must be bit-identical -- a scan must not depend on the
-    size of the batch it was computed in."""
+@pytest.mark.parametrize("dtype,agents,N", [("fp32", 1, 1500), ("fp64", 1, 1500), ("fp64", 2, 1500), ("fp32", 2, 1500),
+                                            ("fp32", 1, 900), ("fp64", 1, 900), ("fp32", 1, 4000), ("fp64", 1, 4000), ("fp64", 2, 3000)])
+def test_small_batch_split_scans_do_not_change_results(dtype, agents, N):
+    """Small launches (F110_SPLIT_BELOW*) share a scan between 8, 4 or 2 warps of a CTA (N * agents = 900: 8, 1500 / 3000:
+    4, 4000 / 6000: 2 on a 148-SM GPU); raycast_variant=128 keeps one warp per scan.  Same arithmetic per beam, so states,
+    flags and scans must be bit-identical -- a scan must not depend on the size of the batch it was computed in."""
     from red_gym_b200 import BatchF110Env
     from red_gym_b200.host import raceline_poses
     import torch
-    N, T = 1500, 80
+    T = 80
     lead = raceline_poses(N)
     poses = [lead]
     for a in range(1, agents):
