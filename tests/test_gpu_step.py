@@ -315,10 +315,11 @@ def test_spatial_launch_order_does_not_change_results(dtype, agents):
 
 
 @pytest.mark.parametrize("dtype,agents,N", [("fp32", 1, 1500), ("fp64", 1, 1500), ("fp64", 2, 1500), ("fp32", 2, 1500),
-                                            ("fp32", 1, 900), ("fp64", 1, 900), ("fp32", 1, 4000), ("fp64", 1, 4000), ("fp64", 2, 3000)])
+                                            ("fp32", 1, 900), ("fp64", 1, 900), ("fp32", 1, 4000), ("fp64", 1, 4000), ("fp64", 2, 3000),
+                                            ("fp32", 1, 200), ("fp64", 2, 120)])
 def test_small_batch_split_scans_do_not_change_results(dtype, agents, N):
-    """Small launches (F110_SPLIT_BELOW*) share a scan between 8, 4 or 2 warps of a CTA (N * agents = 900: 8, 1500 / 3000:
-    4, 4000 / 6000: 2 on a 148-SM GPU); raycast_variant=128 keeps one warp per scan.  Same arithmetic per beam, so states,
+    """Small launches (F110_SPLIT_BELOW*) share a scan between 8, 4 or 2 warps of a CTA (N * agents = 200 / 240 / 900: 8,
+    1500 / 3000: 4, 4000 / 6000: 2 on a 148-SM GPU); raycast_variant=128 keeps one warp per scan.  Same arithmetic per beam, so states,
     flags and scans must be bit-identical -- a scan must not depend on the size of the batch it was computed in."""
     from red_gym_b200 import BatchF110Env
     from red_gym_b200.host import raceline_poses
