@@ -227,6 +227,50 @@ def test_step_host_matches_device_step():
     assert (a.done.cpu() == done).all()
 
 
+@pytest.mark.parametrize("dtype,agents", [("fp64", 1), ("fp64", 2), ("fp32", 1)])
+def test_step_host_small_batch_paths_agree(dtype, agents):
+    """f110_step_host on a handful of envs: with page-locked mapped buffers the kernels read the actions from and
+    write the observation to host memory directly; with pageable (numpy) buffers the copy engines are used; both must
+    return the bytes of a device-side f110_step."""
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    import torch
+    N, T = 5, 25
+    kw = dict(map=os.path.join(MAPS, "example_map"), num_agents=agents, num_envs=N, dtype=dtype,
+              noise="philox" if dtype == "fp32" else "numpy")
+    envs = [BatchF110Env(**kw) for _ in range(3)]
+    lead = raceline_poses(N)
+    poses = [lead]
+    for a in range(1, agents):
+        c = lead.copy()
+        c[:, 0] -= 1.2 * a * np.cos(lead[:, 2]); c[:, 1] -= 1.2 * a * np.sin(lead[:, 2])
+        poses.append(c)
+    poses = np.stack(poses, axis=1)
+    for e in envs:
+        e.reset(poses)
+    sdt = torch.float32 if dtype == "fp32" else torch.float64
+    pin = dict(act=torch.zeros((N, agents, 2), dtype=torch.float64).pin_memory(), obs=torch.zeros((10, N, agents), dtype=torch.float64).pin_memory(),
+               scans=torch.zeros((N, agents, 1080), dtype=sdt).pin_memory(), done=torch.zeros((N,), dtype=torch.uint8).pin_memory())
+    pag = dict(act=np.zeros((N, agents, 2)), obs=np.zeros((10, N, agents)), scans=np.zeros((N, agents, 1080), dtype=np.float32 if dtype == "fp32" else np.float64),
+               done=np.zeros((N,), dtype=np.uint8))
+    rng = np.random.default_rng(3)
+    launches0 = [e.launch_count for e in envs]
+    for t in range(T):
+        a = np.stack([rng.uniform(-0.3, 0.3, (N, agents)), rng.uniform(0.0, 7.0, (N, agents))], axis=-1)
+        envs[0].step(a)
+        pin["act"].numpy()[...] = a
+        envs[1].step_host(pin["act"], pin["obs"], pin["scans"], pin["done"])
+        pag["act"][...] = a
+        envs[2].step_host(pag["act"], pag["obs"], pag["scans"], pag["done"])
+        ref_obs, ref_scans, ref_done = envs[0].obs_block.cpu().numpy(), envs[0].scans.cpu().numpy(), envs[0].done.cpu().numpy()
+        for got in (pin, pag):
+            assert (np.asarray(got["obs"]).reshape(ref_obs.shape) == ref_obs).all(), t
+            assert (np.asarray(got["scans"]) == ref_scans).all(), t
+            assert (np.asarray(got["done"]).astype(bool) == ref_done.astype(bool)).all(), t
+    # the mapped path really ran: one more launch per step (k_export_host) than the copy path
+    assert (envs[1].launch_count - launches0[1]) == (envs[2].launch_count - launches0[2]) + T
+
+
 def test_sharded_run_is_bit_identical_to_unsharded():
     """envs are independent, so splitting N envs over G handles (GPUs) must not change any per-env result --
     including the Philox noise stream and the auto-reset pose choice, both keyed by the GLOBAL env id (env_offset)."""
