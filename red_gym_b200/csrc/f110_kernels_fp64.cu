@@ -263,6 +263,29 @@ struct __align__(16) Scan64 {
 // (laser_models.py:180-184) and truncates; the closed form t0 + i*inc differs from that running
 // sum by < 2160 * 2^-43 < 3e-10, so int() can only differ within 1e-9 of an integer -- those beams
 // replay the sequential sum exactly.
+// The reference's running sum itself (theta_index += increment; wrap), for the beams whose closed form is too close to
+// an integer to trust.  Not as rare as 4e-9 per beam suggests: a car stopped by iTTC has yaw == 0 exactly (check_ttc
+// zeroes it), which puts the LAST beam of a 2 pi scan on an integer -- every scan of every crashed car replays B - 1
+// additions.  The additions are the reference's, in its order; the wrap test after each of them is skipped for stretches
+// in which it cannot fire (t + n * inc stays 2 increments below theta_dis), which leaves a bare chain of DADDs.
+// Out of line: it must not cost the beam loop registers.
+static __device__ __noinline__ int theta_index_replay(double t, int i, double inc, double td)
+{
+    int j = 0;
+    while (j < i) {
+        int n = (int)__ddiv_rn(td - t, inc) - 2;
+        n = min(n, i - j);
+        for (int k = 0; k < n; k++) t += inc;
+        if (n > 0) j += n;
+        if (j < i) {
+            t += inc;
+            while (t >= td) t -= td;
+            j++;
+        }
+    }
+    return (int)t;
+}
+
 static __device__ __forceinline__ int theta_index_of(const F110Dev &d, const Scan64 *c, int i, double a)
 {
     // a ~ t0 + i*inc (closed form, accumulated per round: a few 1e-12 off at most)
@@ -271,14 +294,7 @@ static __device__ __forceinline__ int theta_index_of(const F110Dev &d, const Sca
     double tz = __dadd_rz(a, 4194304.0);
     unsigned lo = (unsigned)__double2loint(tz), hi = (unsigned)__double2hiint(tz);
     int k = (int)(__funnelshift_l(lo, hi, 2) & 0x3FFFFFu);
-    if (((lo + 2u) & 0x3FFFFFFFu) < 4u) {
-        double t = c->t0;
-        for (int j = 0; j < i; j++) {
-            t += d.theta_inc;
-            while (t >= td) t -= td;
-        }
-        return (int)t;
-    }
+    if (((lo + 2u) & 0x3FFFFFFFu) < 4u) return theta_index_replay(c->t0, i, d.theta_inc, td);
     while (k >= d.theta_dis) k -= d.theta_dis;
     return k;
 }
