@@ -94,6 +94,11 @@ class BatchF110Env(object):
 
     # ------------------------------------------------------------------ setup
     def _stream(self):
+        # torch's current stream of this device as a raw cudaStream_t.  torch.cuda.current_stream() builds a Stream object
+        # per call (~8 us, a tenth of a single-env step); the raw accessor behind it is used where this torch has it.
+        raw = getattr(self._torch._C, "_cuda_getCurrentRawStream", None)
+        if raw is not None:
+            return ctypes.c_void_p(raw(self.device_index))
         return ctypes.c_void_p(self._torch.cuda.current_stream(self.device).cuda_stream)
 
     def _upload_map(self, m):
