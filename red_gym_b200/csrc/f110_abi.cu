@@ -564,7 +564,14 @@ static int enqueue_step(f110_sim *s, const uint8_t *mask_dev, cudaStream_t st)
     F110Dev &d = s->d;
     d.step_mask = mask_dev;
     f110_launch_dynamics(d, st);
-    if (d.order) { f110_launch_order(d, st); s->launches += 3; }
+    if (d.order) {
+        // one launch over all envs: sort them as ONE chunk (f110_step_host sorts per copy-out chunk); a single sweep over
+        // the map instead of one per chunk is worth 2 % of the ray-cast at 2^20 envs
+        F110Dev whole = d;
+        whole.order_chunk_envs = d.n_envs;
+        f110_launch_order(whole, st);
+        s->launches += 3;
+    }
     if (s->timing) cudaEventRecord(s->ev_a, st);
     if (d.scan_is_f32) f110_launch_raycast32(d, 0, d.n_envs, s->cfg.raycast_variant, st);
     else f110_launch_raycast64(d, 0, d.n_envs, s->cfg.raycast_variant, st);

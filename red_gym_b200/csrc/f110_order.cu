@@ -126,7 +126,7 @@ void f110_launch_order(const F110Dev &d, cudaStream_t st)
     k_order_count<<<(NA + 255) / 256, 256, 0, st>>>(d, d.state, d.state + NA, d.state + 4 * (size_t)NA, 1, NA, d.n_agents,
                                                     d.order_chunk_envs, d.order_key, d.order_rank);
     const int chunks = (d.n_envs + d.order_chunk_envs - 1) / d.order_chunk_envs;
-    launch_order_scan(chunks, d.order_hist, d.order_base, d.order_bins / chunks, d.order_chunk_envs * d.n_agents, st);
+    launch_order_scan(chunks, d.order_hist, d.order_base, d.order_tx * d.order_ty * 8, d.order_chunk_envs * d.n_agents, st);
     k_order_scatter<<<(NA + 255) / 256, 256, 0, st>>>(d.order_base, d.order_key, d.order_rank, d.order, NA);
 }
 
