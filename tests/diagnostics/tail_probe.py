@@ -1,10 +1,10 @@
 #!/usr/bin/env python
 """Diagnostic (uses the oracle to count lookups per scan, so it is NOT product code): how much of the mid-size batch
 inefficiency of the ray-cast is the spread of per-scan cost?  Times f110_raycast over the same set of raceline poses
-(with lateral/heading jitter) in natural, random and longest-first order.   python tools/tail_probe.py"""
+(with lateral/heading jitter) in natural, random and longest-first order.   python tests/diagnostics/tail_probe.py"""
 import os, sys
 import numpy as np
-REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REPO = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, REPO); sys.path.insert(0, os.path.join(REPO, "oracle"))
 import torch
 import f110_oracle as fo
