@@ -73,8 +73,10 @@ def _p(a):
 
 
 # ---------------------------------------------------------------------------------- host setup
-def load_map(map_path, map_ext):
-    """ScanSimulator2D.set_map (laser_models.py:383-427): flip, threshold at 128, yaml, scipy EDT."""
+def load_map(map_path, map_ext, origin_yaw=None):
+    """ScanSimulator2D.set_map (laser_models.py:383-427): flip, threshold at 128, yaml, scipy EDT.
+    origin_yaw: use this instead of the yaml's origin[2] (every bundled yaml has 0; the rotated goldens of
+    oracle/gen_golden.py were made from a yaml that differs in this one number)."""
     import yaml
     from PIL import Image
     from scipy.ndimage import distance_transform_edt
@@ -85,7 +87,9 @@ def load_map(map_path, map_ext):
     with open(map_path, "r") as f:
         meta = yaml.safe_load(f)
     res = meta["resolution"]
-    origin = meta["origin"]
+    origin = list(meta["origin"])
+    if origin_yaw is not None:
+        origin[2] = float(origin_yaw)
     dt = res * distance_transform_edt(img)        # laser_models.py:40-53
     return dict(dt=np.ascontiguousarray(dt), h=img.shape[0], w=img.shape[1], res=float(res),
                 ox=float(origin[0]), oy=float(origin[1]), oc=float(np.cos(origin[2])), os=float(np.sin(origin[2])))
@@ -139,7 +143,7 @@ class OracleEnv(object):
 
     def __init__(self, num_envs=1, num_agents=2, map=None, map_ext=".png", params=None, timestep=0.01, ego_idx=0,
                  integrator="RK4", fov=2 * np.pi, seed=12345, num_beams=1080, noise=True, noise_rows=2048,
-                 nthreads=0, map_data=None):
+                 nthreads=0, map_data=None, origin_yaw=None):
         with np.errstate(divide="ignore"):
             self.params = dict(DEFAULT_PARAMS if params is None else params)
             self.N, self.A, self.B = num_envs, num_agents, num_beams
@@ -150,7 +154,7 @@ class OracleEnv(object):
             self.h = L.f110o_create(num_envs, num_agents, num_beams, integ, ego_idx, 2000, timestep, fov, 1e-4, 30.0, 0.005)
             if not self.h:
                 raise ValueError("f110o_create failed")
-            self.map = map_data if map_data is not None else load_map(map + ".yaml" if not map.endswith(".yaml") else map, map_ext)
+            self.map = map_data if map_data is not None else load_map(map + ".yaml" if not map.endswith(".yaml") else map, map_ext, origin_yaw)
             m = self.map
             L.f110o_set_map(self.h, _p(m["dt"]), m["h"], m["w"], m["res"], m["ox"], m["oy"], m["oc"], m["os"])
             s, c = trig_tables(2000)

@@ -40,6 +40,44 @@ def _ref():
     return ref_shim.install()
 
 
+def _rot_tag(yaw):
+    return ("rot%+.1f" % yaw).replace("+", "p").replace("-", "m").replace(".", "d")
+
+
+def rotated_map(map_name, yaw):
+    """The bundled map with origin[2] = yaw: a temporary yaml + a copy of the same image (every bundled yaml has
+    yaw 0, so the rotation of xy_2_rc, laser_models.py:75-76 with orig_s/orig_c from :421-422, is otherwise never
+    exercised).  Returns the path without extension, as F110Env's `map` kwarg wants it."""
+    import shutil
+    import yaml
+    d = "/tmp/f110_rot_maps"
+    os.makedirs(d, exist_ok=True)
+    with open(MAPS[map_name] + ".yaml") as f:
+        meta = yaml.safe_load(f)
+    base = os.path.join(d, "%s_%s" % (map_name, _rot_tag(yaw)))
+    meta["origin"] = [float(meta["origin"][0]), float(meta["origin"][1]), float(yaw)]
+    meta["image"] = os.path.basename(base) + ".png"
+    with open(base + ".yaml", "w") as f:
+        yaml.safe_dump(meta, f)
+    shutil.copyfile(MAPS[map_name] + ".png", base + ".png")
+    return base
+
+
+def to_rotated_world(poses, map_name, yaw):
+    """Poses given in the world frame of the unrotated map -> the same places of the track in the world frame of the
+    map whose origin is rotated by yaw (world = origin + R(yaw) * (old - origin), heading + yaw)."""
+    import yaml
+    with open(MAPS[map_name] + ".yaml") as f:
+        o = yaml.safe_load(f)["origin"]
+    c, s = np.cos(yaw), np.sin(yaw)
+    out = np.array(poses, dtype=np.float64)
+    dx, dy = out[..., 0] - o[0], out[..., 1] - o[1]
+    out[..., 0] = o[0] + dx * c - dy * s
+    out[..., 1] = o[1] + dx * s + dy * c
+    out[..., 2] = out[..., 2] + yaw
+    return out
+
+
 def waypoint_poses(n, offset=0.0):
     """n start poses on the example_map raceline: rows k*R/n, (x, y, psi+pi/2)."""
     wp = np.loadtxt(REF + "/examples/example_waypoints.csv", delimiter=";", skiprows=3)
@@ -52,16 +90,16 @@ def waypoint_poses(n, offset=0.0):
 
 
 # ----------------------------------------------------------------------------- scans
-def gen_scans(map_name, fov_name, beams=1080, n_poses=20):
+def gen_scans(map_name, fov_name, beams=1080, n_poses=20, yaw=0.0):
     _ref()
     from f110_gym.envs.laser_models import ScanSimulator2D
     fov = FOVS[fov_name]
     sim = ScanSimulator2D(beams, fov)
-    sim.set_map(MAPS[map_name] + ".yaml", ".png")
+    sim.set_map((rotated_map(map_name, yaw) if yaw else MAPS[map_name]) + ".yaml", ".png")
     rng = np.random.default_rng(7)
     free = np.argwhere(sim.dt > 0.3)
     pick = free[rng.choice(free.shape[0], n_poses, replace=False)]
-    # cell centre -> world (origin yaw is 0 for every bundled map)
+    # cell -> map frame (yaw 0: also the world frame; rotated below)
     x = sim.orig_x + (pick[:, 1] + rng.uniform(0, 1, n_poses)) * sim.map_resolution
     y = sim.orig_y + (pick[:, 0] + rng.uniform(0, 1, n_poses)) * sim.map_resolution
     th = rng.uniform(-2 * np.pi, 4 * np.pi, n_poses)   # includes negative / >2pi yaw (wrap path)
@@ -85,15 +123,23 @@ def gen_scans(map_name, fov_name, beams=1080, n_poses=20):
         [x[0], y[0], fov / 2.0],
     ])
     poses = np.concatenate([poses, extra], axis=0)
+    if yaw:
+        poses = to_rotated_world(poses, map_name, yaw)
+        poses[-2:, 2] = [0.0, fov / 2.0]          # keep the two exact-heading cases exact
     scans = np.stack([sim.scan(p, None) for p in poses])
-    out = os.path.join(GOLDEN, "scans_%s_%s_b%d.npz" % (map_name, fov_name, beams))
-    np.savez_compressed(out, poses=poses, scans=scans, fov=fov, beams=beams, map=map_name)
+    if yaw:
+        out = os.path.join(GOLDEN, "scans_%s_%s_b%d_%s.npz" % (map_name, fov_name, beams, _rot_tag(yaw)))
+        np.savez_compressed(out, poses=poses, scans=scans, fov=fov, beams=beams, map=map_name, origin_yaw=yaw)
+        assert (scans[:n_poses] < 29.0).any(axis=1).mean() > 0.5      # the poses do sit inside the rotated track
+    else:
+        out = os.path.join(GOLDEN, "scans_%s_%s_b%d.npz" % (map_name, fov_name, beams))
+        np.savez_compressed(out, poses=poses, scans=scans, fov=fov, beams=beams, map=map_name)
     print("wrote", out, scans.shape)
 
 
 # ----------------------------------------------------------------------------- rollouts
 def _rollout(tag, map_name, num_agents, integrator_name, fov_name, n_envs, n_steps, poses0, actions,
-             scan_every, seed=12345, params=None, timestep=0.01, ego_idx=0, agent_params=None):
+             scan_every, seed=12345, params=None, timestep=0.01, ego_idx=0, agent_params=None, origin_yaw=0.0):
     """agent_params: {agent index: params dict} applied through F110Env.update_params(params, index) after
     construction (base_classes.py:507-527)."""
     gym = _ref()
@@ -113,8 +159,8 @@ def _rollout(tag, map_name, num_agents, integrator_name, fov_name, n_envs, n_ste
     scans = np.zeros((n_envs, scan_steps.size, A, 1080))
     scan_sum = np.zeros((n_envs, n_steps + 1, A))
     scan_min = np.zeros((n_envs, n_steps + 1, A))
-    kw = dict(map=MAPS[map_name], map_ext=".png", num_agents=A, timestep=timestep, integrator=integ, fov=fov, seed=seed,
-              ego_idx=ego_idx)
+    kw = dict(map=rotated_map(map_name, origin_yaw) if origin_yaw else MAPS[map_name], map_ext=".png", num_agents=A,
+              timestep=timestep, integrator=integ, fov=fov, seed=seed, ego_idx=ego_idx)
     if params is not None:
         kw["params"] = params
     for e in range(n_envs):
@@ -147,9 +193,11 @@ def _rollout(tag, map_name, num_agents, integrator_name, fov_name, n_envs, n_ste
             rec(t + 1, obs, d)
     out = os.path.join(GOLDEN, tag + ".npz")
     extra = {}
+    if origin_yaw:
+        extra["origin_yaw"] = origin_yaw
     if agent_params:
         keys = sorted(next(iter(agent_params.values())).keys())
-        extra = dict(agent_param_idx=np.array(sorted(agent_params)), agent_param_keys=np.array(keys),
+        extra.update(agent_param_idx=np.array(sorted(agent_params)), agent_param_keys=np.array(keys),
                      agent_param_vals=np.array([[agent_params[a][k] for k in keys] for a in sorted(agent_params)]))
     np.savez_compressed(out, map=map_name, num_agents=A, integrator=integrator_name, fov=fov, seed=seed,
                         timestep=timestep, ego_idx=ego_idx, **extra, poses0=poses0, actions=actions, states=S, obs_pose=obs_pose, collisions=coll,
@@ -252,6 +300,87 @@ def gen_rollout_a2_ego1():
              timestep=0.02, ego_idx=1, agent_params={0: p0})
 
 
+def gen_rollout_a2_rot():
+    # head-to-head pairs on example_map with the map origin rotated by -1.2 rad: the rotation of xy_2_rc under the whole
+    # step (lidar, iTTC, opponent ray-cast, laps); same relative placement as rollout_a2_rk4
+    n, T, yaw = 6, 400, -1.2
+    rng = np.random.default_rng(40)
+    lead = waypoint_poses(n)
+    chase = lead.copy()
+    lat = rng.uniform(-0.3, 0.3, n)
+    chase[:, 0] += -1.5 * np.cos(lead[:, 2]) - lat * np.sin(lead[:, 2])
+    chase[:, 1] += -1.5 * np.sin(lead[:, 2]) + lat * np.cos(lead[:, 2])
+    poses0 = to_rotated_world(np.stack([lead, chase], axis=1), "example_map", yaw)
+    act = np.zeros((T, n, 2, 2))
+    act[..., 0] = rng.uniform(-0.15, 0.15, (T // 20 + 1, n, 2)).repeat(20, axis=0)[:T]
+    act[:, :, 0, 1] = rng.uniform(0.0, 4.0, (T // 20 + 1, n)).repeat(20, axis=0)[:T]
+    act[:, :, 1, 1] = rng.uniform(2.0, 8.0, (T // 20 + 1, n)).repeat(20, axis=0)[:T]
+    _rollout("rollout_a2_rot_m1d2", "example_map", 2, "RK4", "2pi", n, T, poses0, act, 100, origin_yaw=yaw)
+
+
+def gen_rollout_a1_rot():
+    # single cars on berlin (resolution 0.05: the exact-division fallback of the cell index) with origin yaw 0.3, Euler
+    n, T, yaw = 4, 300, 0.3
+    base = np.array([[0.0, 0.0, 1.2], [0.0, 0.0, -1.0], [0.3, -0.2, 4.5], [-0.2, 0.1, 0.2]])
+    poses0 = to_rotated_world(base, "berlin", yaw)[:, None, :]
+    act = _random_actions(T, n, 1, seed=12, speed_hi=5.0, hold=10)
+    _rollout("rollout_a1_rot_p0d3_berlin", "berlin", 1, "Euler", "4p7", n, T, poses0, act, 100, seed=778, origin_yaw=yaw)
+
+
+def config2_stream(n_total=4096, n_steps=1000):
+    """start poses k * R / 4096 on the raceline; per step per env steer ~ U(-0.4189, 0.4189),
+    speed ~ U(0, 8) from default_rng(2024) (drawn as in tests/test_gpu_step.py::test_config2_*)."""
+    poses = waypoint_poses(n_total)[:, None, :]
+    rng = np.random.default_rng(2024)
+    actions = np.stack([rng.uniform(-0.4189, 0.4189, (n_steps, n_total, 1)), rng.uniform(0.0, 8.0, (n_steps, n_total, 1))], axis=-1)
+    return poses, actions
+
+
+def gen_config2_slice():
+    """256 of the 4096 envs of BASELINE config 2 (every 16th), all 1000 steps, through the unmodified reference.
+    Compact: flags / toggles at every step, states every 50 steps, scan sums every 10, full scans of 32 envs at 3 steps."""
+    gym = _ref()
+    from f110_gym.envs.base_classes import Integrator
+    stride, T = 16, 1000
+    poses, actions = config2_stream(4096, T)
+    poses, actions = poses[::stride], actions[:, ::stride]
+    n = poses.shape[0]
+    st_steps = np.arange(0, T + 1, 50)
+    sum_steps = np.arange(0, T + 1, 10)
+    sc_steps = np.array([0, 500, 1000])
+    sc_envs = np.arange(0, n, 8)
+    S = np.zeros((n, st_steps.size, 7))
+    coll = np.zeros((n, T + 1), dtype=np.uint8)
+    tog = np.zeros((n, T + 1), dtype=np.int8)
+    done = np.zeros((n, T + 1), dtype=np.uint8)
+    lapt = np.zeros((n, st_steps.size))
+    ssum = np.zeros((n, sum_steps.size))
+    scans = np.zeros((sc_envs.size, sc_steps.size, 1080))
+    env = gym.make("f110_gym:f110-v0", map=MAPS["example_map"], map_ext=".png", num_agents=1, timestep=0.01,
+                   integrator=Integrator.RK4, seed=12345)
+    for e in range(n):
+        def rec(t, obs, d):
+            coll[e, t] = obs["collisions"][0]
+            tog[e, t] = env.toggle_list[0]
+            done[e, t] = d
+            if t % 50 == 0:
+                S[e, t // 50] = env.sim.agents[0].state
+                lapt[e, t // 50] = obs["lap_times"][0]
+            if t % 10 == 0:
+                ssum[e, t // 10] = obs["scans"][0].sum()
+            if e % 8 == 0 and t in (0, 500, 1000):
+                scans[e // 8, (0, 500, 1000).index(t)] = obs["scans"][0]
+        obs, r, d, info = env.reset(poses[e].copy())        # re-seeds the noise stream, clears every counter (f110_env.py:304-347)
+        rec(0, obs, d)
+        for t in range(T):
+            obs, r, d, info = env.step(actions[t, e].copy())
+            rec(t + 1, obs, d)
+    out = os.path.join(GOLDEN, "config2_slice.npz")
+    np.savez_compressed(out, stride=stride, n_total=4096, state_steps=st_steps, states=S, lap_times=lapt, collisions=coll,
+                        toggles=tog, done=done, sum_steps=sum_steps, scan_sum=ssum, scan_steps=sc_steps, scan_envs=sc_envs, scans=scans)
+    print("wrote", out, "envs that hit a wall:", int((coll.max(axis=1) > 0).sum()), "of", n)
+
+
 def gen_waypoint_follow():
     """BASELINE config 1: examples/waypoint_follow.py with render() skipped (GL unavailable on this box)."""
     gym = _ref()
@@ -345,6 +474,9 @@ SCENARIOS = {
     "rollout_a2": gen_rollout_a2,
     "rollout_a3": gen_rollout_a3,
     "rollout_a2_ego1": gen_rollout_a2_ego1,
+    "rollout_a2_rot": gen_rollout_a2_rot,
+    "rollout_a1_rot": gen_rollout_a1_rot,
+    "config2_slice": gen_config2_slice,
     "waypoint_follow": gen_waypoint_follow,
 }
 for _m in MAPS:
@@ -352,6 +484,12 @@ for _m in MAPS:
         SCENARIOS["scans_%s_%s" % (_m, _f)] = (lambda m=_m, f=_f: gen_scans(m, f))
 SCENARIOS["scans_example_map_2pi_b270"] = lambda: gen_scans("example_map", "2pi", beams=270, n_poses=12)
 SCENARIOS["scans_example_map_2pi_b2160"] = lambda: gen_scans("example_map", "2pi", beams=2160, n_poses=6)
+# rotated map origins (the ROT instantiation of the ray-cast had no reference vector)
+SCENARIOS["scans_berlin_2pi_rot_p0d3"] = lambda: gen_scans("berlin", "2pi", yaw=0.3)
+SCENARIOS["scans_berlin_4p7_rot_m1d2"] = lambda: gen_scans("berlin", "4p7", yaw=-1.2)
+SCENARIOS["scans_example_map_2pi_rot_p0d3"] = lambda: gen_scans("example_map", "2pi", yaw=0.3)
+SCENARIOS["scans_example_map_2pi_rot_m1d2"] = lambda: gen_scans("example_map", "2pi", yaw=-1.2)
+SCENARIOS["scans_example_map_2pi_b2160_rot_m1d2"] = lambda: gen_scans("example_map", "2pi", beams=2160, n_poses=6, yaw=-1.2)
 
 
 def main():

@@ -34,11 +34,12 @@ class BatchF110Env(object):
         ego_idx, integrator, fov.
     Batch kwargs: num_envs; device (CUDA ordinal); dtype 'fp64' (parity path) | 'fp32' (fast lidar);
         noise 'numpy' (host PCG64 rows, parity) | 'philox' (device) | 'off'; num_beams (1080);
-        auto_reset + reset_poses (pool [P, A, 3]) for throughput runs; env_offset = global id of env 0 (sharding).
+        auto_reset + reset_poses (pool [P, A, 3]) for throughput runs; env_offset = global id of env 0 (sharding);
+        origin_yaw: replaces origin[2] of the map yaml (map-frame rotation, laser_models.py:421-422).
     """
 
     def __init__(self, num_envs=1, device=0, dtype="fp64", noise=None, num_beams=1080, auto_reset=False,
-                 reset_poses=None, raycast_variant=0, map_data=None, env_offset=0, **kwargs):
+                 reset_poses=None, raycast_variant=0, map_data=None, env_offset=0, origin_yaw=None, **kwargs):
         import torch
         self._torch = torch
         self.lib = nat.load()
@@ -85,7 +86,7 @@ class BatchF110Env(object):
         if map_data is not None:
             self._upload_map(map_data)
         else:
-            self._upload_map(host.MapData(self.map_path, self.map_ext, edt=kwargs.get("edt", "gpu")))
+            self._upload_map(host.MapData(self.map_path, self.map_ext, edt=kwargs.get("edt", "gpu"), origin_yaw=origin_yaw))
         if self.noise == "numpy":
             self._ensure_noise(64)
         if reset_poses is not None:

@@ -32,9 +32,10 @@ def resolve_map(map_name):
 class MapData(object):
     """Occupancy image -> metric EDT (ScanSimulator2D.set_map, laser_models.py:383-427)."""
 
-    def __init__(self, map_path, map_ext, edt="scipy"):
+    def __init__(self, map_path, map_ext, edt="scipy", origin_yaw=None):
         """edt='scipy': get_dt on the host like the reference; edt='gpu': keep only the thresholded image, the library
-        builds the (bit-identical) EDT on the device when the map is uploaded (f110_set_map_image)."""
+        builds the (bit-identical) EDT on the device when the map is uploaded (f110_set_map_image).
+        origin_yaw: replaces the yaml's origin[2] (the map-frame rotation of xy_2_rc, laser_models.py:75-76,421-422)."""
         import yaml
         from PIL import Image
         img_path = os.path.splitext(map_path)[0] + map_ext
@@ -45,7 +46,9 @@ class MapData(object):
         with open(map_path, "r") as stream:
             meta = yaml.safe_load(stream)
         self.resolution = float(meta["resolution"])
-        origin = meta["origin"]
+        origin = list(meta["origin"])
+        if origin_yaw is not None:
+            origin[2] = float(origin_yaw)
         self.origin = (float(origin[0]), float(origin[1]), float(origin[2]))
         self.orig_c = float(np.cos(origin[2]))
         self.orig_s = float(np.sin(origin[2]))

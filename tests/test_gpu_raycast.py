@@ -12,17 +12,31 @@ pytestmark = pytest.mark.gpu
 SCAN_FILES = sorted(glob.glob(os.path.join(GOLDEN, "scans_*.npz")))
 
 
-def _env(map_name, fov, beams, dtype="fp64", variant=0):
+def _env(map_name, fov, beams, dtype="fp64", variant=0, origin_yaw=None):
     from red_gym_b200 import BatchF110Env
     return BatchF110Env(num_envs=1, num_agents=1, map=os.path.join(MAPS, map_name), fov=fov, num_beams=beams,
-                        dtype=dtype, noise="off", raycast_variant=variant)
+                        dtype=dtype, noise="off", raycast_variant=variant, origin_yaw=origin_yaw)
+
+
+def _yaw(d):
+    return float(d["origin_yaw"]) if "origin_yaw" in d.files else None
+
+
+def fp32_error_report(got, want, tag):
+    """The fp32 path's own tolerance, measured and printed (DESIGN.md 2 quotes these): share of beams off by more than
+    2 cm (rays grazing a cell corner take another cell), the largest error, the median."""
+    d = np.abs(np.asarray(got, dtype=np.float64) - want)
+    rep = dict(median=float(np.median(d)), frac_gt_2cm=float((d > 2e-2).mean()), max=float(d.max()), p999=float(np.quantile(d, 0.999)))
+    print("[fp32 tolerance] %s: median %.2e m, > 2 cm: %.4f %% of beams, p99.9 %.3f m, max %.3f m" %
+          (tag, rep["median"], 100 * rep["frac_gt_2cm"], rep["p999"], rep["max"]))
+    return rep
 
 
 @pytest.mark.parametrize("variant", [0, 1])
 @pytest.mark.parametrize("path", SCAN_FILES, ids=[os.path.basename(p)[:-4] for p in SCAN_FILES])
 def test_fp64_scans_match_reference_goldens(path, variant):
     d = np.load(path)
-    env = _env(str(d["map"]), float(d["fov"]), int(d["beams"]), variant=variant)
+    env = _env(str(d["map"]), float(d["fov"]), int(d["beams"]), variant=variant, origin_yaw=_yaw(d))
     out = env.raycast(d["poses"]).cpu().numpy()
     diff = np.abs(out - d["scans"])
     assert diff.max() <= 1e-4        # north_star tolerance
@@ -34,9 +48,46 @@ def _random_poses(m, n, seed):
     rng = np.random.default_rng(seed)
     free = np.argwhere(m["dt"] > 0.15)
     pick = free[rng.integers(0, free.shape[0], n)]
-    x = m["ox"] + (pick[:, 1] + rng.uniform(0, 1, n)) * m["res"]
-    y = m["oy"] + (pick[:, 0] + rng.uniform(0, 1, n)) * m["res"]
+    gx = (pick[:, 1] + rng.uniform(0, 1, n)) * m["res"]
+    gy = (pick[:, 0] + rng.uniform(0, 1, n)) * m["res"]
+    x = m["ox"] + gx * m["oc"] - gy * m["os"]          # map frame -> world (identity for the bundled yamls: yaw 0)
+    y = m["oy"] + gx * m["os"] + gy * m["oc"]
     return np.stack([x, y, rng.uniform(-7, 7, n)], axis=1)
+
+
+@pytest.mark.parametrize("map_name,yaw", [("example_map", 0.3), ("berlin", -1.2), ("vegas", 2.5)])
+def test_rotated_origin_fp64_bit_exact_and_fp32_within_tolerance(map_name, yaw):
+    """xy_2_rc with a rotated map origin (laser_models.py:75-76, orig_s/orig_c from :421-422): the ROT instantiation of
+    k_raycast64 (warp-per-scan and CTA-per-scan), the rotated direction tables of the fp32 path and the rotated key of the
+    spatial sort (40 000 poses > F110_ORDER_FROM).  The oracle is pinned on the scans_*_rot* goldens of the reference."""
+    ora = fo.OracleEnv(1, 1, map=os.path.join(MAPS, map_name), noise=False, origin_yaw=yaw)
+    assert ora.map["os"] != 0.0
+    poses = _random_poses(ora.map, 40000, 21)
+    m = ora.map
+    occ = np.argwhere(m["dt"] == 0.0)[7]
+    gx, gy = (occ[1] + 0.5) * m["res"], (occ[0] + 0.5) * m["res"]
+    poses[:4] = [[m["ox"] - 4.0, m["oy"] + 1.0, 0.3],                                  # outside the map
+                 [m["ox"] + gx * m["oc"] - gy * m["os"], m["oy"] + gx * m["os"] + gy * m["oc"], 1.0],   # on an obstacle
+                 [m["ox"], m["oy"], 0.0], [m["ox"] + 1e4, m["oy"] - 1e4, 2.0]]
+    want, lk = ora.scan(poses, return_lookups=True)
+    assert (want[4:] < 29.0).any(axis=1).mean() > 0.9
+    for variant in (0, 1):
+        env = _env(map_name, 2 * np.pi, 1080, variant=variant, origin_yaw=yaw)
+        env.count_lookups(True)
+        got = env.raycast(poses).cpu().numpy()              # >= 32768 poses: sorted launch, one warp per scan
+        assert (got == want).all(), (variant, np.abs(got - want).max())
+        assert env.lookups() == int(lk.sum()) - poses.shape[0] * (1080 - 1)
+        small = env.raycast(poses[:700]).cpu().numpy()      # CTA-per-scan kernel
+        assert (small == want[:700]).all()
+        plain = _env(map_name, 2 * np.pi, 1080, variant=variant | 64, origin_yaw=yaw).raycast(poses).cpu().numpy()
+        assert (plain == got).all()                         # the sort is only a schedule
+        env.close()
+    f32 = _env(map_name, 2 * np.pi, 1080, dtype="fp32", origin_yaw=yaw)
+    got32 = f32.raycast(poses).cpu().numpy()
+    rep = fp32_error_report(got32[4:], want[4:], "%s origin yaw %+.1f" % (map_name, yaw))
+    assert rep["median"] < 1e-3 and rep["frac_gt_2cm"] < 0.02 and rep["max"] < 2.0
+    assert (f32.raycast(poses[:700]).cpu().numpy() == got32[:700]).all()
+    assert (_env(map_name, 2 * np.pi, 1080, dtype="fp32", variant=64, origin_yaw=yaw).raycast(poses).cpu().numpy() == got32).all()
 
 
 @pytest.mark.parametrize("map_name", ["example_map", "berlin", "skirk", "vegas", "stata_basement"])
@@ -99,9 +150,12 @@ def test_fp32_fast_path_tolerance(map_name, variant):
     want = ora.scan(poses)
     env = _env(map_name, 2 * np.pi, 1080, dtype="fp32", variant=variant)
     got = env.raycast(poses).cpu().numpy().astype(np.float64)
-    d = np.abs(got - want)
-    assert np.median(d) < 1e-3
-    assert (d > 2e-2).mean() < 0.02, (d > 2e-2).mean()
+    rep = fp32_error_report(got, want, "%s variant %d" % (map_name, variant))
+    assert rep["median"] < 1e-3
+    assert rep["frac_gt_2cm"] < 0.02, rep
+    # a ray that takes another cell at a corner runs on to the next wall: the error of such a beam is bounded by the
+    # free path behind the corner, not by the fp32 rounding; observed maxima are a few metres on the corridor maps
+    assert rep["max"] <= 30.0
     assert got.max() <= 30.0 + 1e-3 and got.min() >= 0.0
 
 

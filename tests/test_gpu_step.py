@@ -32,7 +32,8 @@ def test_rollouts_match_reference_goldens(path):
     dt = float(d["timestep"]) if "timestep" in d.files else 0.01
     env = BatchF110Env(num_envs=N, num_agents=A, map=os.path.join(MAPS, str(d["map"])), fov=float(d["fov"]),
                        integrator=str(d["integrator"]), seed=int(d["seed"]), timestep=dt,
-                       ego_idx=int(d["ego_idx"]) if "ego_idx" in d.files else 0)
+                       ego_idx=int(d["ego_idx"]) if "ego_idx" in d.files else 0,
+                       origin_yaw=float(d["origin_yaw"]) if "origin_yaw" in d.files else None)
     if "agent_param_idx" in d.files:        # F110Env.update_params(params, index) after construction
         for a, vals in zip(d["agent_param_idx"], d["agent_param_vals"]):
             env.update_params(dict(zip([str(k) for k in d["agent_param_keys"]], vals)), index=int(a))
@@ -57,6 +58,27 @@ def test_rollouts_match_reference_goldens(path):
         if t in steps:
             assert np.abs(obs["scans"].cpu().numpy() - d["scans"][:, steps.index(t)]).max() <= SCAN_TOL, t
     assert (info["checkpoint_done"].cpu().numpy() == (d["toggles"][:, -1] >= 4)).all()
+
+
+def test_config2_slice_matches_reference_golden():
+    """256 of config 2's 4096 envs (every 16th) x 1000 steps against what the UNMODIFIED reference produced for them
+    (tests/golden/config2_slice.npz): flags, toggles, done bit-exact at every step; states <= 1e-9 relative
+    every 50 steps; scan sums every 10 steps and full scans at three steps <= 1e-4 m.  CUDA's sin/cos/tan are <= 2 ulp from
+    glibc's, so an env may cross a discontinuity (iTTC threshold, kinematic switch) one step apart: such envs are listed."""
+    from red_gym_b200 import BatchF110Env
+    from test_oracle_golden import check_config2_slice, load_config2_slice
+    d = load_config2_slice()
+    n = d["_poses"].shape[0]
+    env = BatchF110Env(num_envs=n, num_agents=1, map=os.path.join(MAPS, "example_map"), seed=12345)
+    env.reset(d["_poses"])
+    names = {"collisions": "collisions", "toggles": "toggle_list", "done": "done", "lap_times": "lap_times", "scans": "scans"}
+
+    def get(name):
+        if name == "state":
+            return _state(env)
+        return getattr(env, names[name]).cpu().numpy()
+    bad = check_config2_slice(env, d, get, REL, SCAN_TOL)
+    assert bad.sum() <= 1, "envs diverged from the reference at a discontinuity: %s" % np.flatnonzero(bad)
 
 
 def _run_against_oracle(N, A, T, poses, actions, check_every, integrator="RK4", seed=12345):
@@ -235,12 +257,72 @@ def test_fp32_path_rollout_tracks_fp64_path():
     # the two paths may see a wall contact one step apart (a range within the fp32 tolerance of the 5 ms iTTC threshold
     # while the car closes in at centimetres per step): a small share of the contacts, and never more than a step
     differ = ~same_flags
-    assert int(differ.sum()) <= int(ever.sum()) // 10, (int(differ.sum()), int(ever.sum()))
-    assert int((first[0][differ] - first[1][differ]).abs().max()) <= 1
+    shift = int((first[0][differ] - first[1][differ]).abs().max()) if bool(differ.any()) else 0
     sa, sb = a.state[:, same_flags], b.state[:, same_flags]
-    assert torch.equal(sa, sb)                             # same flags -> the very same fp64 states (<= 1e-4 rel asked for)
     d = (a.scans[same_flags].double() - b.scans[same_flags].double()).abs()
+    print("[fp32 tolerance] rollout A=1, %d envs x %d steps: %d of %d wall contacts seen one step apart (max shift %d step); "
+          "scans of the other envs: median %.2e m, > 2 cm %.4f %% of beams, max %.3f m" %
+          (N, T, int(differ.sum()), int(ever.sum()), shift, float(d.median()), 100 * float((d > 2e-2).double().mean()), float(d.max())))
+    assert int(differ.sum()) <= int(ever.sum()) // 20, (int(differ.sum()), int(ever.sum()))
+    assert shift <= 1
+    assert torch.equal(sa, sb)                             # same flags -> the very same fp64 states (<= 1e-4 rel asked for)
+    assert float(d.median()) < 1e-3 and float((d > 2e-2).double().mean()) < 0.02 and float(d.max()) <= 30.0
+
+
+@pytest.mark.parametrize("yaw", [None, -1.2])
+def test_fp32_two_agent_rollout_tracks_fp64_path(yaw):
+    """k_agents<float> (GJK on fp64 poses, opponent ray-cast into the fp32 scan) over a whole rollout, not only at reset:
+    head-to-head pairs, fp32 path against the fp64 parity path on the same actions, noise off; also on a rotated map origin.
+    GJK and the lap logic see the same fp64 poses in both paths, so collision_idx / toggles / states are identical for every
+    env whose iTTC flags agree; the opponent shows up in the fp32 scan at the same beams."""
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    import torch
+    N, T = 1024, 150
+    rng = np.random.default_rng(4)
+    lead = raceline_poses(N)
+    lat = rng.uniform(-0.3, 0.3, N)
+    chase = lead.copy()
+    chase[:, 0] += -1.5 * np.cos(lead[:, 2]) - lat * np.sin(lead[:, 2])
+    chase[:, 1] += -1.5 * np.sin(lead[:, 2]) + lat * np.cos(lead[:, 2])
+    poses = np.stack([lead, chase], axis=1)
+    if yaw is not None:        # the same places of the track in the world frame of the rotated map
+        ox, oy = -78.21853769831466, -44.37590462453829
+        c, s_ = np.cos(yaw), np.sin(yaw)
+        dx, dy = poses[..., 0] - ox, poses[..., 1] - oy
+        poses = np.stack([ox + dx * c - dy * s_, oy + dx * s_ + dy * c, poses[..., 2] + yaw], axis=-1)
+    kw = dict(num_envs=N, num_agents=2, map=os.path.join(MAPS, "example_map"), noise="off", origin_yaw=yaw)
+    a, b = BatchF110Env(dtype="fp64", **kw), BatchF110Env(dtype="fp32", **kw)
+    a.reset(poses); b.reset(poses)
+    assert float(a.scans.min()) < 2.0                       # cars are on the track (also in the rotated frame)
+    g = torch.Generator(device="cuda").manual_seed(10)
+    same = torch.ones(N, dtype=torch.bool, device="cuda")
+    gjk = torch.zeros(N, dtype=torch.bool, device="cuda")
+    seen_opp = 0
+    for t in range(T):
+        act = torch.rand((N, 2, 2), generator=g, device="cuda", dtype=torch.float64)
+        act[..., 0] = (act[..., 0] * 2 - 1) * 0.15
+        act[:, 0, 1] = act[:, 0, 1] * 4.0
+        act[:, 1, 1] = 2.0 + act[:, 1, 1] * 6.0
+        a.step(act); b.step(act)
+        same &= (a.in_collision == b.in_collision).all(dim=1)
+        gjk |= (a.collision_idx >= 0).any(dim=1)
+        if t % 25 == 0:
+            # the chaser sees the leader: beams the opponent cast shortened are the same set in both paths (up to the edge beams)
+            da = a.scans[same, 1].double()
+            db = b.scans[same, 1].double()
+            seen_opp += int(((da - db).abs() > 0.5).sum())
+    assert int(gjk.sum()) > N // 20                          # car-car contacts happened
+    assert int((~same).sum()) <= N // 50, int((~same).sum())
+    assert torch.equal(a.state[:, same], b.state[:, same])
+    assert torch.equal(a.collision_idx[same], b.collision_idx[same]) and torch.equal(a.collisions[same], b.collisions[same])
+    assert torch.equal(a.toggle_list[same], b.toggle_list[same])
+    d = (a.scans[same].double() - b.scans[same].double()).abs()
+    print("[fp32 tolerance] rollout A=2 (origin yaw %s), %d envs x %d steps: %d envs with an iTTC flag one step apart; scans: median %.2e m, "
+          "> 2 cm %.4f %% of beams, max %.3f m; GJK fired in %d envs" %
+          (yaw, N, T, int((~same).sum()), float(d.median()), 100 * float((d > 2e-2).double().mean()), float(d.max()), int(gjk.sum())))
     assert float(d.median()) < 1e-3 and float((d > 2e-2).double().mean()) < 0.02
+    assert seen_opp < 0.002 * same.sum().item() * 1080 * (T // 25 + 1)
 
 
 def test_step_host_matches_device_step():
