@@ -23,15 +23,13 @@ def vehicle_dynamics_st(x, u_init, mu, C_Sf, C_Sr, lf, lr, h, m, I, s_min, s_max
 
 
 def accl_constraints(vel, accl, v_switch, a_max, v_min, v_max):
-    """Acceleration limits: row 3 of the kinematic right-hand side is exactly the constrained acceleration."""
-    p = [1.0, 1.0, 1.0, 0.5, 0.5, 0.0, 1.0, 1.0, -1e300, 1e300, -1e300, 1e300, v_switch, a_max, v_min, v_max]
-    return float(_one(_m.dynamics_ks([[0.0, 0.0, 0.0, vel, 0.0]], [[0.0, accl]], p))[3])
+    """Acceleration limits (dynamic_models.py:30-60): the step kernel's own device function (f110_model_accl_constraints)."""
+    return float(_one(_m.accl_constraints(vel, accl, v_switch, a_max, v_min, v_max)))
 
 
 def steering_constraint(steering_angle, steering_velocity, s_min, s_max, sv_min, sv_max):
-    """Steering limits: row 2 of the kinematic right-hand side is exactly the constrained steering velocity."""
-    p = [1.0, 1.0, 1.0, 0.5, 0.5, 0.0, 1.0, 1.0, s_min, s_max, sv_min, sv_max, 1e300, 1e300, -1e300, 1e300]
-    return float(_one(_m.dynamics_ks([[0.0, 0.0, steering_angle, 0.0, 0.0]], [[steering_velocity, 0.0]], p))[2])
+    """Steering limits (dynamic_models.py:63-87): the step kernel's own device function (f110_model_steering_constraint)."""
+    return float(_one(_m.steering_constraint(steering_angle, steering_velocity, s_min, s_max, sv_min, sv_max)))
 
 
 def pid(speed, steer, current_speed, current_steer, max_sv, max_a, max_v, min_v):

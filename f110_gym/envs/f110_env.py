@@ -60,8 +60,10 @@ class F110Env(_Base):
         self.start_thetas = np.zeros((self.num_agents, ))
         self.start_rot = np.eye(2)
 
+        # like the reference (f110_env.py:190) the Simulator is not told the env's ego_idx: obs['ego_idx'] stays 0;
+        # the env-level ego (done flag, lap frame) goes to the library separately
         self.sim = Simulator(self.params, self.num_agents, self.seed, self.sim_car_fov, time_step=self.timestep,
-                             ego_idx=self.ego_idx, integrator=self.integrator, device=kwargs.get('device', 0))
+                             integrator=self.integrator, device=kwargs.get('device', 0), env_ego_idx=self.ego_idx)
         self.sim.set_map(self.map_path, self.map_ext)
         self.render_obs = None
 
@@ -106,9 +108,9 @@ class F110Env(_Base):
         self.start_thetas = poses[:, 2]
         th = self.start_thetas[self.ego_idx]
         self.start_rot = np.array([[np.cos(-th), -np.sin(-th)], [np.sin(-th), np.cos(-th)]])
-        obs = self.sim.reset(poses)          # includes the zero-action step of f110_env.py:335-336
-        self.current_time = self.current_time + self.timestep
-        return self._finish(obs)
+        self.sim.reset(poses)
+        # get no input observations (f110_env.py:335-336)
+        return self.step(np.zeros((self.num_agents, 2)))
 
     def update_map(self, map_path, map_ext):
         self.sim.set_map(map_path, map_ext)

@@ -6,13 +6,11 @@ from red_gym_b200.batch_env import BatchF110Env
 
 
 class ScanSimulator2D(object):
-    """Same constructor, `set_map`, `scan(pose, rng, std_dev)` and `get_increment` as the reference;
-    the ray marching runs on the GPU (f110_raycast).  eps/theta_dis/max_range keep the reference
-    defaults (the C ABI fixes theta_dis=2000)."""
+    """Same constructor, `set_map`, `scan(pose, rng, std_dev)` and `get_increment` as the reference
+    (laser_models.py:360-457); the ray marching runs on the GPU (f110_raycast).  eps, theta_dis and max_range are
+    passed on to the library like any other value of f110_config."""
 
     def __init__(self, num_beams, fov, eps=0.0001, theta_dis=2000, max_range=30.0, device=0):
-        if theta_dis != 2000 or eps != 0.0001 or max_range != 30.0:
-            raise ValueError('only the reference defaults eps=1e-4, theta_dis=2000, max_range=30 are supported')
         self.num_beams = num_beams
         self.fov = fov
         self.eps = eps
@@ -36,7 +34,7 @@ class ScanSimulator2D(object):
         self.orig_c, self.orig_s = m.orig_c, m.orig_s
         self.dt = m.edt
         self._env = BatchF110Env(num_envs=1, num_agents=1, num_beams=self.num_beams, fov=self.fov, noise='off',
-                                 device=self._device, map_data=m)
+                                 device=self._device, map_data=m, eps=self.eps, theta_dis=self.theta_dis, max_range=self.max_range)
         return True
 
     def scan(self, pose, rng, std_dev=0.01):

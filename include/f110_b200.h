@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define F110_ABI_VERSION 1
+#define F110_ABI_VERSION 2
 #define F110_NUM_PARAMS 18   /* order: mu C_Sf C_Sr lf lr h m I s_min s_max sv_min sv_max v_switch a_max
                                 v_min v_max width length  (keys of the params dict, f110_env.py:128) */
 #define F110_MAX_AGENTS 32
@@ -51,6 +51,15 @@ typedef enum {
 #define F110_PRECISION_FP64 0
 #define F110_PRECISION_FP32 1
 
+/* Storage format of the scans (f110_config.scan_format).  NATIVE: double (FP64 path) / float (FP32 path) metres, what
+ * the reference returns (base_classes.py:587-603, converted to the path's type).  U16: opt-in compact observation of the
+ * FP32 path with one agent per env: uint16 at 0.5 mm per LSB (range = value / 2000 m; max_range 30 m = 60000),
+ * converted in the ray-cast epilogue -- half the HBM and PCIe bytes of a float scan; |error| <= 0.25 mm, i.e. 40 x below
+ * the lidar noise of 1 cm; a noisy range below zero is stored as 0. */
+#define F110_SCAN_NATIVE 0
+#define F110_SCAN_U16 1
+#define F110_SCAN_U16_PER_METRE 2000.0
+
 /* Noise source */
 #define F110_NOISE_OFF 0      /* ScanSimulator2D.scan(pose, rng=None) */
 #define F110_NOISE_TABLE 1    /* host-generated rows: row k = k-th draw after reset (base_classes.py:202) */
@@ -71,6 +80,8 @@ typedef struct f110_config {
     int32_t raycast_variant;  /* 0 = default; >0 selects an experimental kernel variant (bench only) */
     int32_t env_offset;       /* global id of this handle's env 0 (env sharding): keys the Philox noise and the reset-pool
                                  choice, so per-env results do not depend on how envs are split over GPUs */
+    int32_t scan_format;      /* F110_SCAN_* */
+    int32_t reserved0;        /* 0 */
     double timestep;          /* f110_env.py:137 */
     double fov;               /* f110_env.py:154-157 */
     double eps;               /* 1e-4  (laser_models.py:360) */
@@ -93,7 +104,7 @@ typedef struct f110_buffers {
     int32_t *toggles;       /* [N][A] toggle_list (f110_env.py:183) */
     uint8_t *done;          /* [N] */
     uint8_t *in_collision;  /* [N][A] iTTC flag (base_classes.py:250) */
-    void *scans;            /* [N][A][B] double (FP64) or float (FP32) */
+    void *scans;            /* [N][A][B] double (FP64), float (FP32) or uint16 (F110_SCAN_U16) */
     double *cur_time;       /* [N] */
     int64_t *noise_step;    /* [N] scans drawn since reset */
     double *actions;        /* [N][A][2] device staging for f110_step_host (may also be written by the caller) */
@@ -144,6 +155,13 @@ int f110_model_vertices(const double *poses_dev, double length, double width, in
 int f110_model_collision(const double *verts_a_dev, const double *verts_b_dev, int64_t n, uint8_t *hit_dev, int device,
                          void *stream);
 
+/* accl_constraints (dynamic_models.py:30-60): in [n][2] = (vel, accl) -> out [n] */
+int f110_model_accl_constraints(const double *in_dev, double v_switch, double a_max, double v_min, double v_max, int64_t n,
+                                double *out_dev, int device, void *stream);
+/* steering_constraint (dynamic_models.py:63-87): in [n][2] = (steering_angle, steering_velocity) -> out [n] */
+int f110_model_steering_constraint(const double *in_dev, double s_min, double s_max, double sv_min, double sv_max, int64_t n,
+                                   double *out_dev, int device, void *stream);
+
 /* Trig tables (laser_models.py:379-381, theta_dis entries) and per-beam tables
  * (base_classes.py:120-156, n_beams entries), computed by the host exactly as the reference does. */
 int f110_set_tables(f110_sim *sim, const double *sines, const double *cosines, const double *scan_angles,
@@ -164,6 +182,11 @@ int f110_set_reset_pool(f110_sim *sim, const double *poses, int32_t n_poses, voi
  * step.  poses: host [N][A][3]; start_rot: host [N][4] row-major 2x2 rotation by -theta_ego as the
  * reference computes it (:329), or NULL to compute it on the device; mask: host [N] bytes or NULL. */
 int f110_reset(f110_sim *sim, const double *poses, const double *start_rot, const uint8_t *mask, void *stream);
+
+/* Simulator.reset (base_classes.py:607-623) on its own: agent states, steering FIFOs, collision flags and the noise
+ * stream are reset to `poses` (host [N][A][3]; start_rot, mask: as in f110_reset) -- WITHOUT the zero-action step that
+ * F110Env.reset adds (f110_env.py:335-336).  The env-level counters (time, lap toggles) are cleared as well. */
+int f110_reset_poses(f110_sim *sim, const double *poses, const double *start_rot, const uint8_t *mask, void *stream);
 
 /* F110Env.step -> Simulator.step (f110_env.py:261-302, base_classes.py:546-605) for all envs.
  * actions_dev: DEVICE [N][A][2] doubles (steer, speed), or NULL to use buffers.actions. */
@@ -192,6 +215,11 @@ int f110_count_lookups(f110_sim *sim, int32_t enable);
  * stream; f110_last_raycast_ms waits for that launch and returns its device time in milliseconds. */
 int f110_enable_timing(f110_sim *sim, int32_t enable);
 int f110_last_raycast_ms(f110_sim *sim, float *ms);
+/* Measurement: read bandwidth of this GPU's L2 by two microbenchmarks over a table of `table_bytes` that stays L2-resident
+ * (L1 bypassed): whole 128-byte lines per warp, and random 4-byte gathers (one 32-byte sector per lane and request: an EDT
+ * lookup that misses L1).  out6: stream GB/s, gather sectors/s, ms per stream launch, ms per gather launch, bytes per
+ * stream launch, sectors per gather launch.  Synchronous.  (the roof the ray-cast is put against.) */
+int f110_l2_probe(int device, int64_t table_bytes, int32_t repeats, double *out6, void *stream);
 /* Number of kernel launches issued by this handle since creation. */
 int64_t f110_launch_count(f110_sim *sim);
 int f110_synchronize(f110_sim *sim, void *stream);

@@ -137,6 +137,22 @@ def gen_scans(map_name, fov_name, beams=1080, n_poses=20, yaw=0.0):
     print("wrote", out, scans.shape)
 
 
+def gen_scans_many_beams(beams=20001):
+    """A beam count far above the env's 1080: theta_index_increment ~ 0.1, so the reference's running sum
+    (laser_models.py:180-184) passes an integer every ten beams and its accumulated rounding decides int() -- the case
+    the product's closed-form beam index has to replay exactly (f110_kernels_fp64.cu: theta_index_of)."""
+    _ref()
+    from f110_gym.envs.laser_models import ScanSimulator2D
+    sim = ScanSimulator2D(beams, 2 * np.pi)
+    sim.set_map(MAPS["example_map"] + ".yaml", ".png")
+    p = waypoint_poses(3)
+    poses = np.array([[p[0, 0], p[0, 1], 0.0], [p[1, 0], p[1, 1], 1.2345678], [p[2, 0], p[2, 1], np.pi]])
+    scans = np.stack([sim.scan(q, None) for q in poses])
+    out = os.path.join(GOLDEN, "scans_example_map_2pi_b%d.npz" % beams)
+    np.savez_compressed(out, poses=poses, scans=scans, fov=2 * np.pi, beams=beams, map="example_map")
+    print("wrote", out, scans.shape)
+
+
 # ----------------------------------------------------------------------------- rollouts
 def _rollout(tag, map_name, num_agents, integrator_name, fov_name, n_envs, n_steps, poses0, actions,
              scan_every, seed=12345, params=None, timestep=0.01, ego_idx=0, agent_params=None, origin_yaw=0.0):
@@ -484,6 +500,7 @@ for _m in MAPS:
         SCENARIOS["scans_%s_%s" % (_m, _f)] = (lambda m=_m, f=_f: gen_scans(m, f))
 SCENARIOS["scans_example_map_2pi_b270"] = lambda: gen_scans("example_map", "2pi", beams=270, n_poses=12)
 SCENARIOS["scans_example_map_2pi_b2160"] = lambda: gen_scans("example_map", "2pi", beams=2160, n_poses=6)
+SCENARIOS["scans_example_map_2pi_b20001"] = gen_scans_many_beams
 # rotated map origins (the ROT instantiation of the ray-cast had no reference vector)
 SCENARIOS["scans_berlin_2pi_rot_p0d3"] = lambda: gen_scans("berlin", "2pi", yaw=0.3)
 SCENARIOS["scans_berlin_4p7_rot_m1d2"] = lambda: gen_scans("berlin", "4p7", yaw=-1.2)

@@ -13,16 +13,26 @@ import sys
 import types
 
 REFERENCE_ROOT = os.environ.get("F110_REFERENCE_ROOT", "/root/reference")
+INSTALLED = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")     # oracle/install_ref.py
+
+
+def package_parent():
+    """Directory to put on sys.path so that `import f110_gym` finds the reference: the reference tree when it is there
+    (build container), else the unmodified copy oracle/install_ref.py placed under oracle/_ref (GPU box)."""
+    for parent in (os.path.join(REFERENCE_ROOT, "gym"), INSTALLED):
+        if os.path.isfile(os.path.join(parent, "f110_gym", "envs", "f110_env.py")):
+            return parent
+    return None
 
 
 def available() -> bool:
-    return os.path.isdir(os.path.join(REFERENCE_ROOT, "gym", "f110_gym"))
+    return package_parent() is not None
 
 
 def install():
     """Make `import f110_gym` resolve to the reference package."""
     if not available():
-        raise RuntimeError("reference tree not present at %s" % REFERENCE_ROOT)
+        raise RuntimeError("reference not present at %s nor under %s" % (REFERENCE_ROOT, INSTALLED))
     os.environ.setdefault("NUMBA_CACHE_DIR", "/tmp/f110_ref_numba_cache")
     if "gym" not in sys.modules:
         gym = types.ModuleType("gym")
@@ -57,7 +67,7 @@ def install():
         pyglet.gl = gl
         sys.modules["pyglet"] = pyglet
         sys.modules["pyglet.gl"] = gl
-    ref_pkg = os.path.join(REFERENCE_ROOT, "gym")
+    ref_pkg = package_parent()
     # our own drop-in package is also called f110_gym: the reference must win here
     for name in [k for k in sys.modules if k == "f110_gym" or k.startswith("f110_gym.")]:
         del sys.modules[name]

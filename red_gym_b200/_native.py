@@ -9,7 +9,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libf110_b200.so")
 
-F110_ABI_VERSION = 1
+F110_ABI_VERSION = 2
 NUM_PARAMS = 18
 PARAM_KEYS = ["mu", "C_Sf", "C_Sr", "lf", "lr", "h", "m", "I", "s_min", "s_max", "sv_min", "sv_max",
               "v_switch", "a_max", "v_min", "v_max", "width", "length"]
@@ -17,16 +17,19 @@ OK, ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_NOMEM = 0, -1, -2, -3, -4
 INTEGRATOR_RK4, INTEGRATOR_EULER = 1, 2
 PRECISION_FP64, PRECISION_FP32 = 0, 1
 NOISE_OFF, NOISE_TABLE, NOISE_PHILOX = 0, 1, 2
+SCAN_NATIVE, SCAN_U16 = 0, 1
+SCAN_U16_PER_METRE = 2000.0
 
 # every symbol include/f110_b200.h declares (tests check the library exports all of them)
 EXPORTS = ["f110_last_error", "f110_abi_version", "f110_device_count", "f110_create", "f110_destroy",
            "f110_set_map", "f110_set_map_image", "f110_edt_build", "f110_set_tables", "f110_set_params", "f110_set_noise_rows", "f110_set_reset_pool",
-           "f110_reset", "f110_step", "f110_step_host", "f110_raycast", "f110_get_buffers", "f110_get_config",
-           "f110_count_lookups", "f110_enable_timing", "f110_last_raycast_ms", "f110_launch_count", "f110_synchronize",
+           "f110_reset", "f110_reset_poses", "f110_step", "f110_step_host", "f110_raycast", "f110_get_buffers", "f110_get_config",
+           "f110_count_lookups", "f110_enable_timing", "f110_last_raycast_ms", "f110_l2_probe", "f110_launch_count", "f110_synchronize",
            "f110_bitmap_create", "f110_bitmap_destroy", "f110_bitmap_render",
            "f110_pursuit_create", "f110_pursuit_destroy", "f110_pursuit_plan",
            "f110_render_create", "f110_render_destroy", "f110_render_frame",
-           "f110_model_dynamics_st", "f110_model_dynamics_ks", "f110_model_pid", "f110_model_vertices", "f110_model_collision"]
+           "f110_model_dynamics_st", "f110_model_dynamics_ks", "f110_model_pid", "f110_model_accl_constraints",
+           "f110_model_steering_constraint", "f110_model_vertices", "f110_model_collision"]
 BITMAP_MODES = {"FILL": 0, "POLYGON": 1, "RAYS": 2}
 
 
@@ -35,6 +38,7 @@ class Config(ctypes.Structure):
                 ("n_beams", ctypes.c_int32), ("integrator", ctypes.c_int32), ("ego_idx", ctypes.c_int32),
                 ("theta_dis", ctypes.c_int32), ("precision", ctypes.c_int32), ("noise_mode", ctypes.c_int32),
                 ("auto_reset", ctypes.c_int32), ("raycast_variant", ctypes.c_int32), ("env_offset", ctypes.c_int32),
+                ("scan_format", ctypes.c_int32), ("reserved0", ctypes.c_int32),
                 ("timestep", ctypes.c_double), ("fov", ctypes.c_double), ("eps", ctypes.c_double),
                 ("max_range", ctypes.c_double), ("ttc_thresh", ctypes.c_double), ("noise_std", ctypes.c_double),
                 ("seed", ctypes.c_uint64)]
@@ -89,6 +93,7 @@ def load():
     L.f110_set_noise_rows.argtypes = [vp, vp, i64, i64, vp]
     L.f110_set_reset_pool.argtypes = [vp, vp, i32, vp]
     L.f110_reset.argtypes = [vp, vp, vp, vp, vp]
+    L.f110_reset_poses.argtypes = [vp, vp, vp, vp, vp]
     L.f110_step.argtypes = [vp, vp, vp]
     L.f110_step_host.argtypes = [vp, vp, vp, vp, vp, vp]
     L.f110_raycast.argtypes = [vp, vp, i32, vp, vp]
@@ -97,6 +102,7 @@ def load():
     L.f110_count_lookups.argtypes = [vp, i32]
     L.f110_enable_timing.argtypes = [vp, i32]
     L.f110_last_raycast_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
+    L.f110_l2_probe.argtypes = [ctypes.c_int, i64, i32, vp, vp]
     L.f110_launch_count.argtypes = [vp]
     L.f110_launch_count.restype = i64
     L.f110_synchronize.argtypes = [vp, vp]
@@ -112,6 +118,8 @@ def load():
     L.f110_model_dynamics_st.argtypes = [vp, vp, vp, i64, vp, ctypes.c_int, vp]
     L.f110_model_dynamics_ks.argtypes = [vp, vp, vp, i64, vp, ctypes.c_int, vp]
     L.f110_model_pid.argtypes = [vp, f64, f64, f64, f64, i64, vp, ctypes.c_int, vp]
+    L.f110_model_accl_constraints.argtypes = [vp, f64, f64, f64, f64, i64, vp, ctypes.c_int, vp]
+    L.f110_model_steering_constraint.argtypes = [vp, f64, f64, f64, f64, i64, vp, ctypes.c_int, vp]
     L.f110_model_vertices.argtypes = [vp, f64, f64, i64, vp, ctypes.c_int, vp]
     L.f110_model_collision.argtypes = [vp, vp, i64, vp, ctypes.c_int, vp]
     for name in EXPORTS:

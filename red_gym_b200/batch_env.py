@@ -35,11 +35,17 @@ class BatchF110Env(object):
     Batch kwargs: num_envs; device (CUDA ordinal); dtype 'fp64' (parity path) | 'fp32' (fast lidar);
         noise 'numpy' (host PCG64 rows, parity) | 'philox' (device) | 'off'; num_beams (1080);
         auto_reset + reset_poses (pool [P, A, 3]) for throughput runs; env_offset = global id of env 0 (sharding);
-        origin_yaw: replaces origin[2] of the map yaml (map-frame rotation, laser_models.py:421-422).
+        origin_yaw: replaces origin[2] of the map yaml (map-frame rotation, laser_models.py:421-422);
+        scan_format 'native' | 'u16' (fp32 path, one agent: scans stored as uint16 at 0.5 mm per LSB, see F110_SCAN_U16).
+
+    Aliasing contract: every tensor this class returns (`scans`, `state`, the observation dict of reset/step, `done`, ...)
+    is a zero-copy VIEW of a device buffer the library owns and overwrites in place on the next reset/step; keep a
+    `.clone()` of whatever must outlive the step (replay buffers, n-step returns), or pass `copy=True` to step/reset.
+    After close() the views are dropped (the memory behind them is freed).
     """
 
     def __init__(self, num_envs=1, device=0, dtype="fp64", noise=None, num_beams=1080, auto_reset=False,
-                 reset_poses=None, raycast_variant=0, map_data=None, env_offset=0, origin_yaw=None, **kwargs):
+                 reset_poses=None, raycast_variant=0, map_data=None, env_offset=0, origin_yaw=None, scan_format="native", **kwargs):
         import torch
         self._torch = torch
         self.lib = nat.load()
@@ -53,6 +59,10 @@ class BatchF110Env(object):
         self.ego_idx = kwargs.get("ego_idx", 0)
         self.integrator = kwargs.get("integrator", "RK4")
         self.fov = kwargs.get("fov", 2 * np.pi)
+        # ScanSimulator2D's own constructor arguments (laser_models.py:360); the env always uses the defaults
+        self.eps = float(kwargs.get("eps", 1e-4))
+        self.theta_dis = int(kwargs.get("theta_dis", 2000))
+        self.max_range = float(kwargs.get("max_range", 30.0))
         self.num_envs = int(num_envs)
         self.num_beams = int(num_beams)
         self.device_index = int(device)
@@ -63,11 +73,15 @@ class BatchF110Env(object):
             noise = "numpy" if dtype == "fp64" else "philox"
         noise_mode = {"off": nat.NOISE_OFF, "numpy": nat.NOISE_TABLE, "philox": nat.NOISE_PHILOX}[noise]
         self.noise = noise
+        if scan_format not in ("native", "u16"):
+            raise ValueError("scan_format must be 'native' or 'u16'")
+        self.scan_format = scan_format
         cfg = nat.Config(abi_version=nat.F110_ABI_VERSION, n_envs=self.num_envs, n_agents=self.num_agents,
                          n_beams=self.num_beams, integrator=_integrator_code(self.integrator), ego_idx=self.ego_idx,
-                         theta_dis=2000, precision=nat.PRECISION_FP64 if dtype == "fp64" else nat.PRECISION_FP32,
+                         theta_dis=self.theta_dis, precision=nat.PRECISION_FP64 if dtype == "fp64" else nat.PRECISION_FP32,
                          noise_mode=noise_mode, auto_reset=1 if auto_reset else 0, raycast_variant=raycast_variant, env_offset=int(env_offset),
-                         timestep=self.timestep, fov=self.fov, eps=1e-4, max_range=30.0, ttc_thresh=0.005,
+                         scan_format=nat.SCAN_U16 if scan_format == "u16" else nat.SCAN_NATIVE, reserved0=0,
+                         timestep=self.timestep, fov=self.fov, eps=self.eps, max_range=self.max_range, ttc_thresh=0.005,
                          noise_std=0.01, seed=self.seed)
         h = ctypes.c_void_p()
         nat.check(self.lib.f110_create(ctypes.byref(cfg), self.device_index, ctypes.byref(h)))
@@ -76,7 +90,7 @@ class BatchF110Env(object):
         self._noise_rows = 0
         self._steps_since_full_reset = 0
         # setup uploads
-        sines, cosines = host.trig_tables(2000)
+        sines, cosines = host.trig_tables(self.theta_dis)
         self.scan_angles, beam_cos, side = host.beam_tables(self.num_beams, self.fov, self.params)
         nat.check(self.lib.f110_set_tables(h, _hp(sines), _hp(cosines), _hp(self.scan_angles), _hp(beam_cos), _hp(side), None))
         pv = host.params_vector(self.params)
@@ -103,13 +117,13 @@ class BatchF110Env(object):
         return ctypes.c_void_p(self._torch.cuda.current_stream(self.device).cuda_stream)
 
     def _upload_map(self, m):
-        self.map = m
         if m.edt is None:      # thresholded image only: get_dt runs on the device (csrc/f110_edt.cu)
             nat.check(self.lib.f110_set_map_image(self._h, _hp(m.free), m.height, m.width, m.resolution, m.origin[0], m.origin[1],
                                                   m.orig_c, m.orig_s, None))
         else:
             nat.check(self.lib.f110_set_map(self._h, _hp(m.edt), m.height, m.width, m.resolution, m.origin[0], m.origin[1],
                                             m.orig_c, m.orig_s, None))
+        self.map = m          # only after the library accepted it: a rejected update leaves the previous map in place
 
     def _ensure_noise(self, rows):
         if self.noise != "numpy" or rows <= self._noise_rows:
@@ -139,7 +153,7 @@ class BatchF110Env(object):
         self.toggle_list = t(b.toggles, (N, A), "<i4")
         self.done = t(b.done, (N,), "|u1")
         self.in_collision = t(b.in_collision, (N, A), "|u1")
-        self.scans = t(b.scans, (N, A, B), "<f8" if self.dtype == "fp64" else "<f4")
+        self.scans = t(b.scans, (N, A, B), "<u2" if self.scan_format == "u16" else "<f8" if self.dtype == "fp64" else "<f4")
         self.current_time = t(b.cur_time, (N,), "<f8")
         self.noise_step = t(b.noise_step, (N,), "<i8")
         self.actions = t(b.actions, (N, A, 2), "<f8")
@@ -167,9 +181,12 @@ class BatchF110Env(object):
         pv = host.params_vector(params)
         nat.check(self.lib.f110_set_params(self._h, _hp(pv), -1 if index < 0 else index, None), IndexError)
 
-    def reset(self, poses, mask=None):
+    def reset(self, poses, mask=None, copy=False, zero_action_step=True):
         """F110Env.reset (f110_env.py:304-347).  poses: (N, A, 3) [x, y, yaw] host array/tensor.
-        mask: optional (N,) bool -- only those envs are reset (the others are untouched)."""
+        mask: optional (N,) bool -- only those envs are reset (the others are untouched).
+        zero_action_step=False: Simulator.reset only (base_classes.py:607-623) -- poses, FIFOs, flags and the noise stream
+        are reset, the zero-action step F110Env.reset adds (:335-336) is left to the caller.
+        Returns views of library buffers (see the class docstring); copy=True returns clones."""
         poses = np.asarray(poses.cpu() if hasattr(poses, "cpu") else poses, dtype=np.float64)
         if poses.ndim == 2 and self.num_envs == 1:
             poses = poses[None]
@@ -185,13 +202,18 @@ class BatchF110Env(object):
         else:
             self._steps_since_full_reset = 0
         self._ensure_noise(2)
+        if not zero_action_step:
+            nat.check(self.lib.f110_reset_poses(self._h, _hp(poses), _hp(rot), _hp(m), self._stream()))
+            return None
         nat.check(self.lib.f110_reset(self._h, _hp(poses), _hp(rot), _hp(m), self._stream()))
         self._steps_since_full_reset += 1
-        return self._obs()
+        return self._obs(copy)
 
-    def step(self, action):
+    def step(self, action, copy=False):
         """F110Env.step (f110_env.py:261-302).  action: (N, A, 2) [steer, speed]; a CUDA float64 tensor is used
-        in place, anything else is copied to the device first."""
+        in place, anything else is copied to the device first.
+        The observation holds VIEWS of library buffers that the next step overwrites (class docstring);
+        copy=True returns clones instead (one extra device copy of the scans per step)."""
         torch = self._torch
         if not isinstance(action, torch.Tensor):
             action = torch.from_numpy(np.ascontiguousarray(np.asarray(action, dtype=np.float64)))
@@ -205,9 +227,13 @@ class BatchF110Env(object):
         self._steps_since_full_reset += 1
         self._ensure_noise(self._steps_since_full_reset + 1)
         nat.check(self.lib.f110_step(self._h, ptr, self._stream()))
-        return self._obs()
+        return self._obs(copy)
 
-    def _obs(self):
+    def _obs(self, copy=False):
+        if copy:
+            obs, reward, done, info = self._obs(False)
+            obs = {k: (v.clone() if hasattr(v, "clone") else v) for k, v in obs.items()}
+            return obs, reward, done.clone(), {"checkpoint_done": info["checkpoint_done"].clone()}
         s = self.state
         obs = {"ego_idx": self.ego_idx, "scans": self.scans, "poses_x": s[0], "poses_y": s[1], "poses_theta": s[4],
                "linear_vels_x": s[3], "linear_vels_y": self._zeros_na, "ang_vels_z": s[5],
@@ -267,6 +293,7 @@ class BatchF110Env(object):
         poses = torch.as_tensor(poses, dtype=torch.float64, device=self.device).contiguous()
         n = poses.shape[0]
         if out is None:
+            # (always float ranges, also for scan_format='u16' handles)
             out = torch.empty((n, self.num_beams), dtype=torch.float64 if self.dtype == "fp64" else torch.float32, device=self.device)
         nat.check(self.lib.f110_raycast(self._h, ctypes.c_void_p(poses.data_ptr()), n, ctypes.c_void_p(out.data_ptr()), self._stream()))
         return out
@@ -303,6 +330,11 @@ class BatchF110Env(object):
             self._render_h = None
         h = getattr(self, "_h", None)
         if h:
+            # the tensors are views of memory f110_destroy frees: drop them (and the DevArray -> env reference cycle)
+            for name in ("state", "obs_block", "collisions", "collision_idx", "lap_times", "lap_counts", "toggle_list", "done",
+                         "in_collision", "scans", "current_time", "noise_step", "actions", "episode_count", "_lookups",
+                         "checkpoint_done", "done_bool"):
+                self.__dict__.pop(name, None)
             self.lib.f110_destroy(h)
             self._h = None
 

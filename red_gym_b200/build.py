@@ -22,6 +22,7 @@ UNITS = [
     ("f110_pursuit.cu", ["-fmad=false"]),
     ("f110_edt.cu", ["-fmad=false"]),
     ("f110_render.cu", ["-fmad=false"]),
+    ("f110_probe.cu", []),
     ("f110_abi.cu", []),
 ]
 

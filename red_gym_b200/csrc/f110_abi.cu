@@ -44,8 +44,6 @@ struct f110_sim {
     size_t rc_order_cap = 0;
     bool use_order = false;
     float2 *dir2 = nullptr;
-    cudaArray_t edt_arr = nullptr;
-    cudaTextureObject_t edt_tex = 0;
     float4 *dir32 = nullptr;
     double *noise = nullptr;
     long long noise_cap = 0;
@@ -59,6 +57,7 @@ struct f110_sim {
     std::vector<cudaEvent_t> chunk_ev;
     long long launches = 0;
     bool timing = false;
+    bool timed = false;            // ev_a / ev_b bracket the ray-cast of the last step
 };
 
 template <typename T>
@@ -111,6 +110,10 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
         return fail(F110_ERR_INVALID, "the fp32 path takes F110_NOISE_OFF or F110_NOISE_PHILOX");
     if (cfg->precision == F110_PRECISION_FP64 && cfg->noise_mode == F110_NOISE_PHILOX)
         return fail(F110_ERR_INVALID, "the fp64 path takes F110_NOISE_OFF or F110_NOISE_TABLE");
+    if (cfg->scan_format != F110_SCAN_NATIVE && cfg->scan_format != F110_SCAN_U16) return fail(F110_ERR_INVALID, "bad scan_format %d", cfg->scan_format);
+    if (cfg->scan_format == F110_SCAN_U16 && (cfg->precision != F110_PRECISION_FP32 || cfg->n_agents != 1 || (cfg->n_beams & 1) ||
+                                              !(cfg->max_range * F110_SCAN_U16_PER_METRE < 65000.0)))
+        return fail(F110_ERR_INVALID, "F110_SCAN_U16 needs the fp32 path, one agent per env, an even beam count and max_range < 32.5 m");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) {
@@ -131,15 +134,26 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
     if (d.n_sm < 1) d.n_sm = 1;
     d.ego_idx = cfg->ego_idx; d.theta_dis = cfg->theta_dis; d.noise_mode = cfg->noise_mode; d.auto_reset = cfg->auto_reset;
     d.scan_is_f32 = cfg->precision == F110_PRECISION_FP32;
+    d.scan_u16 = cfg->scan_format == F110_SCAN_U16;
     d.env_offset = cfg->env_offset;
     d.timestep = cfg->timestep; d.fov = cfg->fov; d.eps = cfg->eps; d.max_range = cfg->max_range;
     d.ttc_thresh = cfg->ttc_thresh; d.noise_std = cfg->noise_std; d.seed = cfg->seed;
     d.noise_std32 = (float)cfg->noise_std; d.ttc_thresh32 = (float)cfg->ttc_thresh;
+    d.noise_k32 = (float)(-2.0 * M_LN2 * cfg->noise_std * cfg->noise_std);
+    if (cfg->noise_mode == F110_NOISE_PHILOX && !(cfg->noise_std > 1e-12)) d.noise_mode = F110_NOISE_OFF;   // sigma 0: nothing to add
     // laser_models.py:367-368
     double angle_increment = cfg->fov / (cfg->n_beams - 1);
     d.theta_inc = cfg->theta_dis * angle_increment / (2. * M_PI);
     d.inc_fix = (unsigned long long)(d.theta_inc * 4294967296.0 + 0.5);
     d.kstep_lo = (unsigned)(32ull * d.inc_fix); d.kstep_hi = (unsigned)((32ull * d.inc_fix) >> 32);
+    // fp64 beam index (theta_index_of): the reference's running sum drifts from the closed form by at most half an ulp of
+    // theta_dis per addition (1.14e-13 at 2000), the closed form itself by an ulp per round of 32 beams; the band within
+    // which the running sum is replayed exactly is that bound in units of 2^-30, plus 2 (3 units = 2.8e-9 up to 2160 beams)
+    {
+        const double ulp = nextafter((double)cfg->theta_dis, 1e300) - (double)cfg->theta_dis;
+        const double drift = 0.5 * ulp * cfg->n_beams + ulp * ((cfg->n_beams + 31) / 32);
+        d.theta_band = 2u + (unsigned)ceil(drift * 1073741824.0);
+    }
     int rc = 0;
     do {
         // obs block: 7 state fields + collisions + lap_times + lap_counts, contiguous for a single D2H copy
@@ -169,7 +183,7 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
         if ((rc = dev_alloc(s, &s->stage_poses, 3 * NA))) break;
         if ((rc = dev_alloc(s, &s->stage_rot, 4 * N))) break;
         if ((rc = dev_alloc(s, &s->stage_mask, N))) break;
-        size_t scan_bytes = NA * B * (d.scan_is_f32 ? 4 : 8);
+        size_t scan_bytes = NA * B * (d.scan_u16 ? 2 : d.scan_is_f32 ? 4 : 8);
         uint8_t *scans = nullptr;
         if ((rc = dev_alloc(s, &scans, scan_bytes, false))) break;
         d.scans = scans;
@@ -225,8 +239,6 @@ extern "C" int f110_destroy(f110_sim *s)
     if (s->order_hist) cudaFree(s->order_hist);
     if (s->order_base) cudaFree(s->order_base);
     if (s->rc_order_buf) cudaFree(s->rc_order_buf);
-    if (s->edt_tex) cudaDestroyTextureObject(s->edt_tex);
-    if (s->edt_arr) cudaFreeArray(s->edt_arr);
     if (s->noise) cudaFree(s->noise);
     if (s->pool) cudaFree(s->pool);
     for (cudaEvent_t ev : s->chunk_ev) cudaEventDestroy(ev);
@@ -239,27 +251,28 @@ extern "C" int f110_destroy(f110_sim *s)
 
 void f110_launch_edt_build(const uint8_t *free_px, unsigned *scratch_g, double *edt, int h, int w, double res, cudaStream_t st);
 
-// edt: host [h][w] metres, or null with free_px: host [h][w] bytes (non-zero = free) to build the EDT on the device
-static int set_map_impl(f110_sim *s, const double *edt, const uint8_t *free_px, int32_t h, int32_t w, double res, double ox,
-                        double oy, double oc, double os, void *stream)
+// Everything a map owns on the device.  set_map_impl builds a new one completely and only then swaps it in: a failed
+// update_map (bad size, out of memory, ...) leaves the handle with its previous map, never with freed pointers.
+struct MapBufs {
+    double *edt64 = nullptr;
+    float *edt32 = nullptr, *edt32p = nullptr;
+    int *order_hist = nullptr, *order_base = nullptr;
+    void release()
+    {
+        cudaFree(edt64); cudaFree(edt32); cudaFree(edt32p); cudaFree(order_hist); cudaFree(order_base);
+        *this = MapBufs();
+    }
+};
+
+static int build_map(f110_sim *s, MapBufs &m, F110Dev &d, const double *edt, const uint8_t *free_px, int32_t h, int32_t w, double res,
+                     double ox, double oy, double oc, double os, cudaStream_t st, int &launches)
 {
-    if (!s || (!edt && !free_px) || h < 1 || w < 1 || !(res > 0)) return fail(F110_ERR_INVALID, "bad map arguments");
-    if (free_px && (h > 65534 || w > 65534)) return fail(F110_ERR_INVALID, "map too large for the device EDT");
-    cudaStream_t st = (cudaStream_t)stream;
-    CK(cudaSetDevice(s->device));
-    CK(cudaStreamSynchronize(st));
-    if (s->edt64) { cudaFree(s->edt64); cudaFree(s->edt32); s->edt64 = nullptr; s->edt32 = nullptr; }
-    if (s->edt32p) { cudaFree(s->edt32p); s->edt32p = nullptr; }
-    if (s->edt_tex) { cudaDestroyTextureObject(s->edt_tex); s->edt_tex = 0; }
-    if (s->edt_arr) { cudaFreeArray(s->edt_arr); s->edt_arr = nullptr; }
-    F110Dev &d = s->d;
-    size_t cells = (size_t)h * w;
-    if (cells >= (1ull << 31)) return fail(F110_ERR_INVALID, "map too large");
-    CK(cudaMalloc(&s->edt64, cells * 8));
-    CK(cudaMalloc(&s->edt32, cells * 4));
+    const size_t cells = (size_t)h * w;
+    CK(cudaMalloc(&m.edt64, cells * 8));
+    CK(cudaMalloc(&m.edt32, cells * 4));
     double last_cell;
     if (edt) {
-        CK(cudaMemcpyAsync(s->edt64, edt, cells * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(m.edt64, edt, cells * 8, cudaMemcpyHostToDevice, st));
         last_cell = edt[cells - 1];
     } else {
         uint8_t *fp = nullptr;
@@ -267,9 +280,9 @@ static int set_map_impl(f110_sim *s, const double *edt, const uint8_t *free_px, 
         CK(cudaMalloc(&fp, cells));
         if (cudaMalloc(&g, cells * 4) != cudaSuccess) { cudaFree(fp); return fail(F110_ERR_NOMEM, "cudaMalloc failed"); }
         cudaMemcpyAsync(fp, free_px, cells, cudaMemcpyHostToDevice, st);
-        f110_launch_edt_build(fp, g, s->edt64, h, w, res, st);
-        s->launches += 2;
-        cudaError_t e1 = cudaMemcpyAsync(&last_cell, s->edt64 + cells - 1, 8, cudaMemcpyDeviceToHost, st);
+        f110_launch_edt_build(fp, g, m.edt64, h, w, res, st);
+        launches += 2;
+        cudaError_t e1 = cudaMemcpyAsync(&last_cell, m.edt64 + cells - 1, 8, cudaMemcpyDeviceToHost, st);
         cudaError_t e2 = cudaStreamSynchronize(st);
         cudaFree(fp); cudaFree(g);
         if (e1 != cudaSuccess || e2 != cudaSuccess) return fail(F110_ERR_CUDA, "device EDT failed: %s", cudaGetErrorString(e2 != cudaSuccess ? e2 : e1));
@@ -287,27 +300,28 @@ static int set_map_impl(f110_sim *s, const double *edt, const uint8_t *free_px, 
     d.sent32 = 1024.0f;
     while (d.sent32 <= cap) d.sent32 *= 2.0f;
     d.oob32 = last_cell > s->cfg.eps ? fminf((float)(last_cell / res), cap) : d.sent32;
-    d.edt64 = s->edt64; d.edt32 = s->edt32;
-    f110_launch_edt32(s->edt64, s->edt32, cells, d.inv_res, s->cfg.eps, cap, d.sent32, st);
-    s->launches += 1;
+    d.edt64 = m.edt64; d.edt32 = m.edt32;
+    f110_launch_edt32(m.edt64, m.edt32, cells, d.inv_res, s->cfg.eps, cap, d.sent32, st);
+    launches += 1;
+    d.edt32p = nullptr; d.edt32p_adj = 0; d.pad = 0; d.wp = 0;
     if (d.scan_is_f32) {   // padded copy for the fp32 ray-cast (see scan32p)
         d.pad = (int)ceil(s->cfg.max_range / res) + 2;
         d.wp = w + 2 * d.pad;
         size_t pcells = (size_t)d.wp * (h + 2 * d.pad);
         if (pcells >= (1ull << 31)) return fail(F110_ERR_INVALID, "map too large for the padded fp32 layout");
-        CK(cudaMalloc(&s->edt32p, pcells * 4));
-        f110_launch_pad_edt32(s->edt32, s->edt32p, h, w, d.pad, d.oob32, st);
-        d.edt32p = s->edt32p;
+        CK(cudaMalloc(&m.edt32p, pcells * 4));
+        f110_launch_pad_edt32(m.edt32, m.edt32p, h, w, d.pad, d.oob32, st);
+        d.edt32p = m.edt32p;
         // index bias of the mantissa-floor trick: bits(2^23 + n) = 0x4B000000 + n
         for (unsigned cx = 0; ; cx += (1u << 21)) {
             uint64_t k = ((uint64_t)0x4B000000u * (uint64_t)d.wp + 0x4B000000u + cx) & 0xffffffffull;
             if (k + pcells < (1ull << 32)) {
                 d.magic_x = 8388608.0f + (float)cx;
-                d.edt32p_adj = (unsigned long long)s->edt32p - 4ull * k;
+                d.edt32p_adj = (unsigned long long)m.edt32p - 4ull * k;
                 break;
             }
         }
-        s->launches += 1;
+        launches += 1;
     }
     {
         // spatial launch order: tiles of >= 32 cells, at most 64 x 64 of them; 8 heading octants; chunk-major
@@ -318,41 +332,60 @@ static int set_map_impl(f110_sim *s, const double *edt, const uint8_t *free_px, 
         d.order_inv_tile = 1.0f / (float)tile;
         int chunks = (d.n_envs + d.order_chunk_envs - 1) / d.order_chunk_envs;
         d.order_bins = chunks * d.order_tx * d.order_ty * 8;
-        if (s->order_hist) { cudaFree(s->order_hist); cudaFree(s->order_base); s->order_hist = s->order_base = nullptr; }
-        CK(cudaMalloc(&s->order_hist, (size_t)d.order_bins * 4));
-        CK(cudaMalloc(&s->order_base, (size_t)d.order_bins * 4));
-        CK(cudaMemsetAsync(s->order_hist, 0, (size_t)d.order_bins * 4, st));
+        CK(cudaMalloc(&m.order_hist, (size_t)d.order_bins * 4));
+        CK(cudaMalloc(&m.order_base, (size_t)d.order_bins * 4));
+        CK(cudaMemsetAsync(m.order_hist, 0, (size_t)d.order_bins * 4, st));
         const size_t NA = (size_t)d.n_envs * d.n_agents;
         if (s->use_order) { d.order = s->order_buf; d.order_key = s->order_buf + NA; d.order_rank = s->order_buf + 2 * NA; }
-        d.order_hist = s->order_hist; d.order_base = s->order_base;
+        d.order_hist = m.order_hist; d.order_base = m.order_base;
     }
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(st));
-    // the same fp32 map as a CUDA array behind a point-sampled texture (2D-local layout, floor + address in the TEX unit)
-    {
-        cudaChannelFormatDesc fd = cudaCreateChannelDesc<float>();
-        CK(cudaMallocArray(&s->edt_arr, &fd, (size_t)w, (size_t)h));
-        CK(cudaMemcpy2DToArray(s->edt_arr, 0, 0, s->edt32, (size_t)w * 4, (size_t)w * 4, (size_t)h, cudaMemcpyDeviceToDevice));
-        cudaResourceDesc rd; memset(&rd, 0, sizeof(rd));
-        rd.resType = cudaResourceTypeArray; rd.res.array.array = s->edt_arr;
-        cudaTextureDesc td; memset(&td, 0, sizeof(td));
-        td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
-        td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
-        CK(cudaCreateTextureObject(&s->edt_tex, &rd, &td, nullptr));
-        d.edt_tex = (unsigned long long)s->edt_tex;
+    return F110_OK;
+}
+
+// edt: host [h][w] metres, or null with free_px: host [h][w] bytes (non-zero = free) to build the EDT on the device
+static int set_map_impl(f110_sim *s, const double *edt, const uint8_t *free_px, int32_t h, int32_t w, double res, double ox,
+                        double oy, double oc, double os, void *stream)
+{
+    if (!s || (!edt && !free_px) || h < 1 || w < 1 || !(res > 0)) return fail(F110_ERR_INVALID, "bad map arguments");
+    if (free_px && (h > 65534 || w > 65534)) return fail(F110_ERR_INVALID, "map too large for the device EDT");
+    if ((size_t)h * w >= (1ull << 31)) return fail(F110_ERR_INVALID, "map too large");
+    // the fp32 map codes "stop here" (distance <= eps) as a sentinel and takes the last step as 0: exact only while no
+    // free cell is that close to a wall, i.e. eps below one cell (the fp64 path takes any eps)
+    if (s->d.scan_is_f32 && !(s->cfg.eps < res)) return fail(F110_ERR_INVALID, "the fp32 path needs eps (%g) below the map resolution (%g)", s->cfg.eps, res);
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(cudaSetDevice(s->device));
+    CK(cudaStreamSynchronize(st));
+    MapBufs fresh;
+    F110Dev nd = s->d;          // the new map's fields are filled into a copy
+    int launches = 0;
+    int rc = build_map(s, fresh, nd, edt, free_px, h, w, res, ox, oy, oc, os, st, launches);
+    s->launches += launches;
+    if (rc) {                   // the handle keeps the map it had (has_map unchanged)
+        cudaStreamSynchronize(st);
+        fresh.release();
+        return rc;
     }
-    s->has_map = true;
     // direction table depends on the map rotation: rebuild if tables are already there
     if (s->has_tables) {
-        std::vector<double> sn(d.theta_dis), cs(d.theta_dis);
-        CK(cudaMemcpy(sn.data(), d.sines, d.theta_dis * 8, cudaMemcpyDeviceToHost));
-        CK(cudaMemcpy(cs.data(), d.cosines, d.theta_dis * 8, cudaMemcpyDeviceToHost));
+        std::vector<double> sn(nd.theta_dis), cs(nd.theta_dis);
+        cudaError_t e1 = cudaMemcpy(sn.data(), nd.sines, nd.theta_dis * 8, cudaMemcpyDeviceToHost);
+        cudaError_t e2 = cudaMemcpy(cs.data(), nd.cosines, nd.theta_dis * 8, cudaMemcpyDeviceToHost);
+        if (e1 != cudaSuccess || e2 != cudaSuccess) { fresh.release(); return fail(F110_ERR_CUDA, "table read-back failed"); }
         std::vector<float4> dir;
         std::vector<float2> dir2;
-        build_dir_table(sn.data(), cs.data(), d.theta_dis, oc, os, dir, dir2);
-        CK(cudaMemcpy(s->dir32, dir.data(), dir.size() * sizeof(float4), cudaMemcpyHostToDevice));
-        CK(cudaMemcpy(s->dir2, dir2.data(), dir2.size() * sizeof(float2), cudaMemcpyHostToDevice));
+        build_dir_table(sn.data(), cs.data(), nd.theta_dis, oc, os, dir, dir2);
+        e1 = cudaMemcpy(s->dir32, dir.data(), dir.size() * sizeof(float4), cudaMemcpyHostToDevice);
+        e2 = cudaMemcpy(s->dir2, dir2.data(), dir2.size() * sizeof(float2), cudaMemcpyHostToDevice);
+        if (e1 != cudaSuccess || e2 != cudaSuccess) { fresh.release(); return fail(F110_ERR_CUDA, "direction table upload failed"); }
     }
+    MapBufs old;
+    old.edt64 = s->edt64; old.edt32 = s->edt32; old.edt32p = s->edt32p; old.order_hist = s->order_hist; old.order_base = s->order_base;
+    s->edt64 = fresh.edt64; s->edt32 = fresh.edt32; s->edt32p = fresh.edt32p; s->order_hist = fresh.order_hist; s->order_base = fresh.order_base;
+    s->d = nd;
+    s->has_map = true;
+    old.release();
     return F110_OK;
 }
 
@@ -434,6 +467,24 @@ extern "C" int f110_model_pid(const double *in_dev, double max_sv, double max_a,
     if (rc) return rc;
     f110_launch_model_pid(in_dev, max_sv, max_a, max_v, min_v, n, out_dev, (cudaStream_t)stream);
     return model_done("pid");
+}
+extern "C" int f110_model_accl_constraints(const double *in_dev, double v_switch, double a_max, double v_min, double v_max, int64_t n,
+                                           double *out_dev, int device, void *stream)
+{
+    if (!in_dev || !out_dev || n < 0) return fail(F110_ERR_INVALID, "bad arguments");
+    int rc = model_device(device);
+    if (rc) return rc;
+    f110_launch_model_constraint(in_dev, v_switch, a_max, v_min, v_max, n, 0, out_dev, (cudaStream_t)stream);
+    return model_done("accl_constraints");
+}
+extern "C" int f110_model_steering_constraint(const double *in_dev, double s_min, double s_max, double sv_min, double sv_max, int64_t n,
+                                              double *out_dev, int device, void *stream)
+{
+    if (!in_dev || !out_dev || n < 0) return fail(F110_ERR_INVALID, "bad arguments");
+    int rc = model_device(device);
+    if (rc) return rc;
+    f110_launch_model_constraint(in_dev, s_min, s_max, sv_min, sv_max, n, 1, out_dev, (cudaStream_t)stream);
+    return model_done("steering_constraint");
 }
 extern "C" int f110_model_vertices(const double *poses_dev, double length, double width, int64_t n, double *verts_dev, int device,
                                    void *stream)
@@ -575,7 +626,7 @@ static int enqueue_step(f110_sim *s, const uint8_t *mask_dev, cudaStream_t st)
     if (s->timing) cudaEventRecord(s->ev_a, st);
     if (d.scan_is_f32) f110_launch_raycast32(d, 0, d.n_envs, s->cfg.raycast_variant, st);
     else f110_launch_raycast64(d, 0, d.n_envs, s->cfg.raycast_variant, st);
-    if (s->timing) cudaEventRecord(s->ev_b, st);
+    if (s->timing) { cudaEventRecord(s->ev_b, st); s->timed = true; }
     s->launches += 2;
     if (d.n_agents > 1) { f110_launch_agents(d, st); s->launches++; }
     f110_launch_finalize(d, st);
@@ -607,6 +658,23 @@ extern "C" int f110_reset(f110_sim *s, const double *poses, const double *start_
     if (rc) return rc;
     // the staging buffers are reused by the next call
     CK(cudaStreamSynchronize(st));
+    return F110_OK;
+}
+
+extern "C" int f110_reset_poses(f110_sim *s, const double *poses, const double *start_rot, const uint8_t *mask, void *stream)
+{
+    TRY(check_ready(s));
+    if (!poses) return fail(F110_ERR_INVALID, "Number of poses for reset does not match number of agents.");
+    CK(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t N = s->d.n_envs, NA = N * s->d.n_agents;
+    CK(cudaMemcpyAsync(s->stage_poses, poses, 3 * NA * 8, cudaMemcpyHostToDevice, st));
+    if (start_rot) CK(cudaMemcpyAsync(s->stage_rot, start_rot, 4 * N * 8, cudaMemcpyHostToDevice, st));
+    if (mask) CK(cudaMemcpyAsync(s->stage_mask, mask, N, cudaMemcpyHostToDevice, st));
+    f110_launch_reset(s->d, s->stage_poses, start_rot ? s->stage_rot : nullptr, mask ? s->stage_mask : nullptr, st);
+    s->launches++;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));      // the staging buffers are reused by the next call
     return F110_OK;
 }
 
@@ -653,7 +721,8 @@ extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *o
     cudaStream_t st = (cudaStream_t)stream;
     F110Dev &d = s->d;
     const size_t N = d.n_envs, A = d.n_agents, NA = N * A, B = d.n_beams;
-    const size_t esz = d.scan_is_f32 ? 4 : 8;
+    const size_t esz = d.scan_u16 ? 2 : d.scan_is_f32 ? 4 : 8;
+    s->timed = false;
     if ((scans_host ? NA * B * esz : 0) + 10 * NA * 8 <= F110_ZERO_COPY_MAX_BYTES) {
         const double *act_d = (const double *)mapped_host_ptr(actions_host);
         double *obs_d = (double *)mapped_host_ptr(obs_block_host);
@@ -664,7 +733,7 @@ extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *o
             int rc = enqueue_step(s, nullptr, st);
             s->d.actions = s->actions;
             if (rc) return rc;
-            const size_t words = NA * B * (esz / 4);
+            const size_t words = NA * B * esz / 4;        // B is even for 2-byte scans (f110_create)
             const int grid = (int)((words / 4 + 255) / 256);
             k_export_host<<<grid < 1 ? 1 : (grid > 64 ? 64 : grid), 256, 0, st>>>(s->obs_block, obs_d, 10 * NA, (const unsigned *)d.scans, scans_d,
                                                                                     words, d.done, done_d, N);
@@ -691,6 +760,7 @@ extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *o
         for (size_t i = old; i < s->chunk_ev.size(); i++) cudaEventCreateWithFlags(&s->chunk_ev[i], cudaEventDisableTiming);
     }
     size_t per = (N + chunks - 1) / chunks;     // == d.order_chunk_envs when the scans are ordered
+    if (s->timing) cudaEventRecord(s->ev_a, st);     // all chunk launches (the copies run on the other stream)
     for (int c = 0; c < chunks; c++) {
         size_t b = c * per, cnt = (b + per <= N) ? per : (N > b ? N - b : 0);
         if (!cnt) break;
@@ -704,6 +774,7 @@ extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *o
                                cudaMemcpyDeviceToHost, s->copy_stream));
         }
     }
+    if (s->timing) { cudaEventRecord(s->ev_b, st); s->timed = true; }
     if (A > 1) { f110_launch_agents(d, st); s->launches++; }
     f110_launch_finalize(d, st);
     s->launches++;
@@ -774,15 +845,29 @@ extern "C" int f110_enable_timing(f110_sim *s, int32_t enable)
 {
     if (!s) return fail(F110_ERR_INVALID, "null handle");
     s->timing = enable != 0;
+    if (!s->timing) s->timed = false;
     return F110_OK;
 }
 
 extern "C" int f110_last_raycast_ms(f110_sim *s, float *ms)
 {
     if (!s || !ms) return fail(F110_ERR_INVALID, "null argument");
+    if (!s->timed) return fail(F110_ERR_STATE, "no timed ray-cast: call f110_enable_timing(sim, 1) before the step");
     CK(cudaSetDevice(s->device));
     CK(cudaEventSynchronize(s->ev_b));
     CK(cudaEventElapsedTime(ms, s->ev_a, s->ev_b));
+    return F110_OK;
+}
+
+extern "C" int f110_l2_probe(int device, int64_t table_bytes, int32_t repeats, double *out6, void *stream)
+{
+    if (!out6 || table_bytes < (1 << 20) || table_bytes > (1ll << 32) || repeats < 1) return fail(F110_ERR_INVALID, "bad probe arguments");
+    int rc = model_device(device);
+    if (rc) return rc;
+    int n_sm = 148;
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+    int r = f110_probe_l2(n_sm, (size_t)table_bytes & ~(size_t)127, repeats, out6, (cudaStream_t)stream);
+    if (r) return fail(r == 1 ? F110_ERR_NOMEM : F110_ERR_CUDA, "L2 probe failed (%s)", cudaGetErrorString(cudaGetLastError()));
     return F110_OK;
 }
 

@@ -38,12 +38,15 @@ static __host__ __device__ __forceinline__ int f110_split_wps(int n, int n_sm)
 struct F110Dev {
     int n_envs, n_agents, n_beams, integrator, ego_idx, theta_dis;
     int noise_mode, auto_reset, count_lookups, n_pool, scan_is_f32, env_offset;
-    int n_sm, pad0_;                   // SMs of the device (split-scan CTA -> scan mapping)
+    int n_sm;                          // SMs of the device (split-scan CTA -> scan mapping)
+    unsigned theta_band;               // fp64 beam index: replay the reference's running sum within this many 2^-30 of an integer
+    int scan_u16, pad1_;               // F110_SCAN_U16: scans stored as uint16 at 0.5 mm per LSB (fp32 path, one agent per env)
     double timestep, fov, eps, max_range, theta_inc, ttc_thresh, noise_std;
     unsigned long long seed;
     unsigned long long inc_fix;        // theta_inc in 32.32 fixed point; kstep = 32 * inc_fix (one round of 32 beams)
     unsigned kstep_lo, kstep_hi;
     float max_c32, res32, noise_std32, ttc_thresh32, side_max32, sent32;   // fp32 path constants (cells / metres)
+    float noise_k32, pad2_;            // -2 ln 2 * noise_std^2 (Box-Muller radius scaled by sigma, see box_muller)
     // map
     int map_h, map_w, res_pow2, has_rot;
     double res, inv_res, ox, oy, oc, os, xmax, ymax;
@@ -52,7 +55,6 @@ struct F110Dev {
     float oob32;
     const double *edt64;               // row-major [h][w], metres
     const float *edt32;                // row-major [h][w], in CELL units (metres / res); obstacle cells hold sent32 (see fp32 kernels)
-    unsigned long long edt_tex;        // cudaTextureObject_t over a CUDA array with the same content (point sampling)
     const float *edt32p;               // edt32 with a border of `pad` cells on every side holding oob32: [h + 2 pad][wp]
     unsigned long long edt32p_adj;     // byte address of edt32p minus 4 * K, K = what the float exponent bits contribute (scan32p)
     float magic_x;                     // 2^23 (+ 2^21 when K would wrap the 32-bit index)
@@ -109,9 +111,11 @@ void f110_launch_edt32(const double *src, float *dst, size_t cells, double inv_r
 void f110_launch_order(const F110Dev &d, cudaStream_t st);      // (chunk, tile, heading) counting sort -> d.order
 void f110_launch_order_poses(const F110Dev &d, const double *poses, int n, int *buf, cudaStream_t st);
 void f110_launch_pad_edt32(const float *src, float *dst, int h, int w, int pad, float oob, cudaStream_t st);
+int f110_probe_l2(int n_sm, size_t table_bytes, int repeats, double *out, cudaStream_t st);      // f110_probe.cu
 
 // model functions on their own (f110_kernels_fp64.cu, end of file)
 void f110_launch_model_dynamics(const double *x, const double *u, const double *p16, long long n, int ks, double *f, cudaStream_t st);
 void f110_launch_model_pid(const double *in, double max_sv, double max_a, double max_v, double min_v, long long n, double *out, cudaStream_t st);
+void f110_launch_model_constraint(const double *in, double a, double b, double c, double e_, long long n, int steering, double *out, cudaStream_t st);
 void f110_launch_model_vertices(const double *poses, double length, double width, long long n, double *verts, cudaStream_t st);
 void f110_launch_model_collision(const double *a, const double *b, long long n, uint8_t *hit, cudaStream_t st);

@@ -261,8 +261,8 @@ struct __align__(16) Scan64 {
 
 // Table index of beam i.  The reference accumulates theta_index += increment beam after beam
 // (laser_models.py:180-184) and truncates; the closed form t0 + i*inc differs from that running
-// sum by < 2160 * 2^-43 < 3e-10, so int() can only differ within 1e-9 of an integer -- those beams
-// replay the sequential sum exactly.
+// sum by < n_beams * 2^-43 (2.5e-10 for 2160 beams), so int() can only differ within a band around the integers
+// that grows with the beam count (theta_band, 2.8e-9 up to 2160 beams) -- those beams replay the sequential sum exactly.
 // The reference's running sum itself (theta_index += increment; wrap), for the beams whose closed form is too close to
 // an integer to trust.  Not as rare as 4e-9 per beam suggests: a car stopped by iTTC has yaw == 0 exactly (check_ttc
 // zeroes it), which puts the LAST beam of a 2 pi scan on an integer -- every scan of every crashed car replays B - 1
@@ -294,7 +294,9 @@ static __device__ __forceinline__ int theta_index_of(const F110Dev &d, const Sca
     double tz = __dadd_rz(a, 4194304.0);
     unsigned lo = (unsigned)__double2loint(tz), hi = (unsigned)__double2hiint(tz);
     int k = (int)(__funnelshift_l(lo, hi, 2) & 0x3FFFFFu);
-    if (((lo + 2u) & 0x3FFFFFFFu) < 4u) return theta_index_replay(c->t0, i, d.theta_inc, td);
+    // band = d.theta_band units of 2^-30 on either side of an integer: covers the drift of the reference's running sum
+    // (<= half an ulp of 2048 = 1.1e-13 per addition) for the handle's beam count, see f110_create
+    if (((lo + d.theta_band) & 0x3FFFFFFFu) < 2u * d.theta_band) return theta_index_replay(c->t0, i, d.theta_inc, td);
     while (k >= d.theta_dis) k -= d.theta_dis;
     return k;
 }
@@ -1085,6 +1087,14 @@ __global__ void __launch_bounds__(128) k_model_pid(const double *__restrict__ in
     pid_ctrl(in[4 * i], in[4 * i + 1], in[4 * i + 2], in[4 * i + 3], max_sv, max_a, max_v, min_v, accl, sv);
     out[2 * i] = accl; out[2 * i + 1] = sv;
 }
+// accl_constraints (:30-60) / steering_constraint (:63-87) on their own: in [n][2] -> out [n]
+__global__ void __launch_bounds__(128) k_model_constraint(const double *__restrict__ in, double a, double b, double c, double e_,
+                                                          long long n, int steering, double *__restrict__ out)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = steering ? steering_constraint(in[2 * i], in[2 * i + 1], a, b, c, e_) : accl_constraints(in[2 * i], in[2 * i + 1], a, b, c, e_);
+}
 // get_vertices (collision_models.py:238-260): poses [n][3] -> corners [n][4][2]
 __global__ void __launch_bounds__(128) k_model_vertices(const double *__restrict__ poses, double length, double width, long long n,
                                                         double *__restrict__ verts)
@@ -1121,6 +1131,10 @@ void f110_launch_model_dynamics(const double *x, const double *u, const double *
 void f110_launch_model_pid(const double *in, double max_sv, double max_a, double max_v, double min_v, long long n, double *out, cudaStream_t st)
 {
     if (n > 0) k_model_pid<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(in, max_sv, max_a, max_v, min_v, n, out);
+}
+void f110_launch_model_constraint(const double *in, double a, double b, double c, double e_, long long n, int steering, double *out, cudaStream_t st)
+{
+    if (n > 0) k_model_constraint<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(in, a, b, c, e_, n, steering, out);
 }
 void f110_launch_model_vertices(const double *poses, double length, double width, long long n, double *verts, cudaStream_t st)
 {

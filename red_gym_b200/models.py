@@ -77,6 +77,27 @@ def pid(speed, steer, current_speed, current_steer, max_sv, max_a, max_v, min_v,
     return out[:, 0], out[:, 1]
 
 
+def _constraint(fn, a, b, limits, device):
+    import torch
+    dev = _dev(device)
+    cols = [_t(v, (), dev) for v in (a, b)]
+    n = max(c.shape[0] for c in cols)
+    inp = torch.stack([c.expand(n) for c in cols], dim=1).contiguous()
+    out = torch.empty((n,), dtype=torch.float64, device=dev)
+    nat.check(getattr(nat.load(), fn)(_vp(inp), *[float(v) for v in limits], n, _vp(out), dev.index, _stream(dev)))
+    return out
+
+
+def accl_constraints(vel, accl, v_switch, a_max, v_min, v_max, device=None):
+    """accl_constraints (dynamic_models.py:30-60) for n (velocity, acceleration) pairs -> (n,)."""
+    return _constraint("f110_model_accl_constraints", vel, accl, (v_switch, a_max, v_min, v_max), device)
+
+
+def steering_constraint(steering_angle, steering_velocity, s_min, s_max, sv_min, sv_max, device=None):
+    """steering_constraint (dynamic_models.py:63-87) for n (angle, velocity) pairs -> (n,)."""
+    return _constraint("f110_model_steering_constraint", steering_angle, steering_velocity, (s_min, s_max, sv_min, sv_max), device)
+
+
 def get_vertices(poses, length, width, device=None):
     """get_vertices for n poses (n, 3) -> corners (n, 4, 2) in the reference's order rl, rr, fr, fl."""
     import torch

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
 def test_config_struct_matches_header_layout():
     from red_gym_b200 import _native as nat
     # 12 int32 + 6 double + 1 uint64
-    assert ctypes.sizeof(nat.Config) == 12 * 4 + 6 * 8 + 8
+    assert ctypes.sizeof(nat.Config) == 14 * 4 + 6 * 8 + 8
     assert ctypes.sizeof(nat.Buffers) == 16 * ctypes.sizeof(ctypes.c_void_p)
 
 

@@ -140,7 +140,7 @@ def test_edge_poses():
     assert tuple(empty.shape) == (0, 1080)
 
 
-@pytest.mark.parametrize("variant", [0, 4])
+@pytest.mark.parametrize("variant", [0, 128])
 @pytest.mark.parametrize("map_name", ["example_map", "berlin", "vegas"])
 def test_fp32_fast_path_tolerance(map_name, variant):
     """fp32 lidar: own tolerance: median error < 1 mm; > 2 cm only where a ray grazes a cell
@@ -163,9 +163,9 @@ def test_fp32_variants_agree():
     ora = fo.OracleEnv(1, 1, map=os.path.join(MAPS, "example_map"), noise=False)
     poses = _random_poses(ora.map, 500, 9)
     a = _env("example_map", 2 * np.pi, 1080, dtype="fp32", variant=0).raycast(poses).cpu().numpy()
-    b = _env("example_map", 2 * np.pi, 1080, dtype="fp32", variant=4).raycast(poses).cpu().numpy()
-    # variant 4 fetches through the texture unit (same cells, same arithmetic)
-    assert (np.abs(a - b) > 1e-3).mean() < 1e-3
+    b = _env("example_map", 2 * np.pi, 1080, dtype="fp32", variant=128).raycast(poses).cpu().numpy()
+    # variant 128 keeps one warp per scan where the default shares a scan between the warps of a CTA: same arithmetic per beam
+    assert (a == b).all()
 
 
 def test_scan_before_map_raises_like_reference():
@@ -236,7 +236,7 @@ def test_fp32_sentinel_and_cap_scale_with_the_map(size, res):
 @pytest.mark.gpu
 def test_fp32_philox_noise_is_gaussian_and_independent():
     """The fp32 path replaces the reference's numpy stream (laser_models.py:448-452: rng.normal(0, std_dev, B)) by a
-    counter-based Philox4x32-10 + Box-Muller stream.  Validated on its own: cars at rest (zero action: the pose does not
+    counter-based Philox4x32-7 + Box-Muller stream.  Validated on its own: cars at rest (zero action: the pose does not
     change, vel == 0 switches iTTC off), so noisy scan - noise-free scan is the noise alone."""
     import torch
     from scipy import stats
