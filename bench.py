@@ -286,7 +286,7 @@ def run_b200(args):
                     "note": "algorithmic bytes (SURVEY 8d) over the measured L2 read peak.  The kernel is NOT bound by L2 or HBM bandwidth: "
                             "L1 serves most gathers (l2_sectors / hbm below are what ncu measured leaving L1 / L2); it is bound by the latency "
                             "of its dependent L1-hit gather chain and by issue slots (issue below)"}
-        if prof:
+        if prof and "l2_read_sectors_per_scan" in prof:
             sect = prof["l2_read_sectors_per_scan"] * scans_per_launch
             roofline["l2_sectors"] = {"read_GBps": sect * 32 / rc_s / 1e9, "gather_peak_GBps": l2[tab]["gather_sector_GBps"],
                                       "frac_of_gather_peak": sect / rc_s / l2[tab]["gather_sectors_per_s"],

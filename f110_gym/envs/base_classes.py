@@ -119,6 +119,10 @@ class Simulator(object):
         self._h_obs = torch.zeros((10, A), dtype=torch.float64).pin_memory()
         self._h_scans = torch.zeros((A, 1080), dtype=torch.float64).pin_memory()
         self._h_done = torch.zeros((1,), dtype=torch.uint8).pin_memory()
+        # numpy views and raw addresses of the pinned buffers, made once: a single-env step is ~35 us of GPU work
+        self._np_act, self._np_obs, self._np_scans = self._h_act.numpy(), self._h_obs.numpy(), self._h_scans.numpy()
+        self._np_done = self._h_done.numpy()
+        self._ptrs = (self._h_act.data_ptr(), self._h_obs.data_ptr(), self._h_scans.data_ptr(), self._h_done.data_ptr())
 
     def set_map(self, map_path, map_ext):
         self._map = (map_path, map_ext)
@@ -134,12 +138,12 @@ class Simulator(object):
         self._need_batch().update_params(params, index=agent_idx)
 
     def _collect(self):
-        o = self._h_obs.numpy()
+        o = self._np_obs.copy()                       # (10, A): one copy, then plain views / scalars of it
         A = self.num_agents
-        self.agent_poses = np.stack([o[0], o[1], o[4]], axis=1)
-        self.collisions = o[7].copy()
+        self.agent_poses = o[[0, 1, 4]].T
+        self.collisions = o[7]
         self._collision_idx = None if A > 1 else -1 * np.ones((A,))      # A > 1: fetched from the device on access
-        scans = self._h_scans.numpy()
+        scans = self._np_scans
         observations = {'ego_idx': self.ego_idx,
                         'scans': [scans[i].copy() for i in range(A)],
                         'poses_x': [np.float64(o[0, i]) for i in range(A)],
@@ -149,9 +153,9 @@ class Simulator(object):
                         'linear_vels_y': [0. for _ in range(A)],
                         'ang_vels_z': [np.float64(o[5, i]) for i in range(A)],
                         'collisions': self.collisions}
-        self.lap_times = o[8].copy()
-        self.lap_counts = o[9].copy()
-        self.done = bool(self._h_done[0])
+        self.lap_times = o[8]
+        self.lap_counts = o[9]
+        self.done = bool(self._np_done[0])
         return observations
 
     @property
@@ -164,8 +168,8 @@ class Simulator(object):
     def step(self, control_inputs):
         """Simulator.step (base_classes.py:546-605): one tick of all agents -> observation dict."""
         b = self._need_batch()
-        self._h_act.numpy()[0] = np.asarray(control_inputs, dtype=np.float64).reshape(self.num_agents, 2)
-        b.step_host(self._h_act, self._h_obs, self._h_scans, self._h_done)
+        self._np_act[0] = np.asarray(control_inputs, dtype=np.float64).reshape(self.num_agents, 2)
+        b.step_host_ptrs(*self._ptrs)
         return self._collect()
 
     def reset(self, poses):

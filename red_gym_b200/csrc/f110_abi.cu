@@ -609,11 +609,30 @@ static int check_ready(f110_sim *s)
     return 0;
 }
 
-// kernels of one step, in the order of Simulator.step + F110Env.step
-static int enqueue_step(f110_sim *s, const uint8_t *mask_dev, cudaStream_t st)
+static bool use_fused(const f110_sim *s)
+{
+    const F110Dev &d = s->d;
+    return !d.scan_is_f32 && d.n_agents == 1 && d.n_envs <= F110_FUSED_MAX_ENVS && !(s->cfg.raycast_variant & (128 | 256));   // variant bits 7 / 8: three-kernel step
+}
+
+// kernels of one step, in the order of Simulator.step + F110Env.step.  host_*: mapped host buffers the fused
+// small-batch kernel may write the observation to directly (all null: device buffers only)
+static int enqueue_step(f110_sim *s, const uint8_t *mask_dev, cudaStream_t st, double *host_obs = nullptr, double *host_scans = nullptr,
+                        uint8_t *host_done = nullptr, bool *exported = nullptr)
 {
     F110Dev &d = s->d;
     d.step_mask = mask_dev;
+    if (exported) *exported = false;
+    if (use_fused(s)) {
+        if (s->timing) cudaEventRecord(s->ev_a, st);
+        f110_launch_step_fused64(d, host_obs, host_scans, host_done, st);
+        if (s->timing) { cudaEventRecord(s->ev_b, st); s->timed = true; }
+        s->launches++;
+        d.step_mask = nullptr;
+        if (exported) *exported = true;
+        CK(cudaGetLastError());
+        return 0;
+    }
     f110_launch_dynamics(d, st);
     if (d.order) {
         // one launch over all envs: sort them as ONE chunk (f110_step_host sorts per copy-out chunk); a single sweep over
@@ -730,14 +749,17 @@ extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *o
         uint8_t *done_d = (uint8_t *)mapped_host_ptr(done_host);
         if (act_d && (obs_d || !obs_block_host) && (scans_d || !scans_host) && (done_d || !done_host)) {
             s->d.actions = act_d;
-            int rc = enqueue_step(s, nullptr, st);
+            bool exported = false;
+            int rc = enqueue_step(s, nullptr, st, obs_d, (double *)scans_d, done_d, &exported);
             s->d.actions = s->actions;
             if (rc) return rc;
-            const size_t words = NA * B * esz / 4;        // B is even for 2-byte scans (f110_create)
-            const int grid = (int)((words / 4 + 255) / 256);
-            k_export_host<<<grid < 1 ? 1 : (grid > 64 ? 64 : grid), 256, 0, st>>>(s->obs_block, obs_d, 10 * NA, (const unsigned *)d.scans, scans_d,
-                                                                                    words, d.done, done_d, N);
-            s->launches++;
+            if (!exported) {
+                const size_t words = NA * B * esz / 4;        // B is even for 2-byte scans (f110_create)
+                const int grid = (int)((words / 4 + 255) / 256);
+                k_export_host<<<grid < 1 ? 1 : (grid > 64 ? 64 : grid), 256, 0, st>>>(s->obs_block, obs_d, 10 * NA, (const unsigned *)d.scans, scans_d,
+                                                                                        words, d.done, done_d, N);
+                s->launches++;
+            }
             CK(cudaGetLastError());
             CK(cudaStreamSynchronize(st));
             return F110_OK;
@@ -746,6 +768,14 @@ extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *o
     CK(cudaMemcpyAsync(s->actions, actions_host, 2 * NA * 8, cudaMemcpyHostToDevice, st));
     d.actions = s->actions;
     d.step_mask = nullptr;
+    if (use_fused(s)) {      // pageable host buffers: the fused kernel, then the copy engines
+        TRY(enqueue_step(s, nullptr, st));
+        if (scans_host) CK(cudaMemcpyAsync(scans_host, d.scans, NA * B * esz, cudaMemcpyDeviceToHost, st));
+        if (obs_block_host) CK(cudaMemcpyAsync(obs_block_host, s->obs_block, 10 * NA * 8, cudaMemcpyDeviceToHost, st));
+        if (done_host) CK(cudaMemcpyAsync(done_host, d.done, N, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        return F110_OK;
+    }
     f110_launch_dynamics(d, st);
     s->launches++;
     if (d.order) { f110_launch_order(d, st); s->launches += 3; }

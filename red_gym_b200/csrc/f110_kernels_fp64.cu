@@ -104,11 +104,10 @@ static __device__ __forceinline__ unsigned pool_index(int e, long long episode, 
     return (unsigned)(z % (unsigned long long)n_pool);
 }
 
-__global__ void __launch_bounds__(128) k_dynamics(const F110Dev d)
+// RaceCar.update_pose without the scan (base_classes.py:254-402) for agent ia: steering FIFO, pid, RK4 / Euler, yaw wrap
+static __device__ __forceinline__ void dynamics_agent(const F110Dev &d, int ia)
 {
     const int NA = d.n_envs * d.n_agents;
-    int ia = blockIdx.x * blockDim.x + threadIdx.x;
-    if (ia >= NA) return;
     int e = ia / d.n_agents, a = ia - e * d.n_agents;
     if (d.step_mask && !d.step_mask[e]) return;
 
@@ -184,6 +183,12 @@ __global__ void __launch_bounds__(128) k_dynamics(const F110Dev d)
     d.pose_pre[ia] = x[0];
     d.pose_pre[NA + ia] = x[1];
     d.pose_pre[2 * (size_t)NA + ia] = x[4];
+}
+
+__global__ void __launch_bounds__(128) k_dynamics(const F110Dev d)
+{
+    int ia = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ia < d.n_envs * d.n_agents) dynamics_agent(d, ia);
 }
 
 void f110_launch_dynamics(const F110Dev &d, cudaStream_t st)
@@ -478,9 +483,15 @@ __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int en
     bool hit = false;
     unsigned nlook = 0;
     if (SPLIT) {
-        if (ia >= 0) {
-            scan_rounds_claimed<ROT, POW2, true, COUNT>(d, c, hit, nlook, &next_round[slot], lane == 0 && warp % wps == 0);
-            if (__any_sync(FULL, hit) && lane == 0) atomicOr(&hit_any[slot], 1);
+        // own scan first; a warp whose scan has no rounds left takes rounds of the CTA's other scans (scans differ by 2 x in
+        // their number of lookups, and the CTA ends with its slowest one).  Which warp casts a round changes no result.
+        for (int k = 0; k < per_cta; k++) {
+            int s2 = slot + k;
+            if (s2 >= per_cta) s2 -= per_cta;
+            if (row_ia[s2] < 0) continue;
+            bool h = false;
+            scan_rounds_claimed<ROT, POW2, true, COUNT>(d, rows + s2, h, nlook, &next_round[s2], k == 0 && lane == 0 && warp % wps == 0);
+            if (__any_sync(FULL, h) && lane == 0) atomicOr(&hit_any[s2], 1);
         }
         __syncthreads();                        // every warp has read the state by now
         hit = hit_any[slot] != 0;
@@ -927,10 +938,8 @@ void f110_launch_agents(const F110Dev &d, cudaStream_t st)
 // ------------------------------------------------------------------------------------------------
 // F110Env.step tail: time, _check_done (f110_env.py:202-244, 292-299)
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_finalize(const F110Dev d)
+static __device__ __forceinline__ void finalize_env(const F110Dev &d, int e)
 {
-    int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= d.n_envs) return;
     if (d.step_mask && !d.step_mask[e]) return;
     const int A = d.n_agents, NA = d.n_envs * A;
     double t = d.cur_time[e] + d.timestep;
@@ -973,9 +982,94 @@ __global__ void __launch_bounds__(128) k_finalize(const F110Dev d)
     }
 }
 
+__global__ void __launch_bounds__(128) k_finalize(const F110Dev d)
+{
+    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < d.n_envs) finalize_env(d, e);
+}
+
 void f110_launch_finalize(const F110Dev &d, cudaStream_t st)
 {
     k_finalize<<<(d.n_envs + 127) / 128, 128, 0, st>>>(d);
+}
+
+// ------------------------------------------------------------------------------------------------
+// The whole tick of a single-agent env in ONE kernel (north_star: "dynamics, integration and TTC fused into one per-env
+// kernel"), for a handful of envs: a CTA per env.  Thread 0 integrates the car (dynamics_agent) and prepares the scan, the
+// eight warps cast it (rounds claimed from a shared counter, as in the split kernel), thread 0 applies the iTTC outcome
+// and the lap bookkeeping (finalize_env), and -- when the caller's host buffers are mapped -- the CTA writes the env's
+// observation straight into them.  Same device functions as k_dynamics / k_raycast64 / k_finalize, so the results are
+// bit-identical to the three-kernel step (tests/test_gpu_step.py); what goes away is three launches and their gaps, which
+// dominate a single-env step (one env: 46 us of kernels in an 80 us call before).
+// ------------------------------------------------------------------------------------------------
+struct F110HostOut {
+    double *obs;            // [10][N] or null
+    double *scans;          // [N][B] or null
+    uint8_t *done;          // [N] or null
+};
+
+template <bool ROT, bool POW2, bool COUNT>
+__global__ void __launch_bounds__(256) k_step_fused64(const F110Dev d, const F110HostOut ho)
+{
+    __shared__ Scan64 row;
+    __shared__ int next_round, hit_any, active;
+    const int e = (int)blockIdx.x, lane = threadIdx.x & 31;      // one agent per env: ia == e
+    if (threadIdx.x == 0) {
+        active = !(d.step_mask && !d.step_mask[e]);
+        if (active) {
+            dynamics_agent(d, e);
+            prepare_env_scan64<ROT, POW2>(d, e, &row, true);
+        }
+        next_round = 0;
+        hit_any = 0;
+    }
+    __syncthreads();
+    if (!active) return;
+    bool hit = false;
+    unsigned nlook = 0;
+    scan_rounds_claimed<ROT, POW2, true, COUNT>(d, &row, hit, nlook, &next_round, threadIdx.x == 0);
+    if (__any_sync(FULL, hit) && lane == 0) atomicOr(&hit_any, 1);
+    __syncthreads();
+    const int N = d.n_envs;
+    if (threadIdx.x == 0) {
+        const bool h = hit_any != 0;      // RaceCar.check_ttc (base_classes.py:241-250)
+        if (h) { d.state[3 * (size_t)N + e] = 0.; d.state[4 * (size_t)N + e] = 0.; d.state[5 * (size_t)N + e] = 0.; d.state[6 * (size_t)N + e] = 0.; }
+        d.in_collision[e] = h ? 1 : 0;
+        finalize_env(d, e);
+        if (ho.done) ho.done[e] = d.done[e];
+        if (ho.obs) {
+#pragma unroll
+            for (int k = 0; k < 7; k++) ho.obs[(size_t)k * N + e] = d.state[(size_t)k * N + e];
+            ho.obs[7 * (size_t)N + e] = d.collisions[e];
+            ho.obs[8 * (size_t)N + e] = d.lap_times[e];
+            ho.obs[9 * (size_t)N + e] = d.lap_counts[e];
+        }
+    }
+    if (ho.scans) {       // the scan this CTA just wrote (visible CTA-wide after the barrier) -> the caller's host buffer
+        const double *src = (const double *)d.scans + (size_t)e * d.n_beams;
+        double *dst = ho.scans + (size_t)e * d.n_beams;
+        for (int i = threadIdx.x; i < d.n_beams; i += 256) dst[i] = src[i];
+    }
+    if (COUNT) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) nlook += __shfl_xor_sync(FULL, nlook, o);
+        if (lane == 0) atomicAdd(d.lookups, (unsigned long long)nlook);
+    }
+}
+
+void f110_launch_step_fused64(const F110Dev &d, double *obs_host, double *scans_host, uint8_t *done_host, cudaStream_t st)
+{
+    F110HostOut ho = { obs_host, scans_host, done_host };
+    const bool cnt = d.count_lookups != 0;
+#define FUSED(R, P)                                                                   \
+    do {                                                                              \
+        if (cnt) k_step_fused64<R, P, true><<<d.n_envs, 256, 0, st>>>(d, ho);         \
+        else k_step_fused64<R, P, false><<<d.n_envs, 256, 0, st>>>(d, ho);            \
+    } while (0)
+    if (d.has_rot) FUSED(true, false);
+    else if (d.res_pow2) FUSED(false, true);
+    else FUSED(false, false);
+#undef FUSED
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -260,10 +260,10 @@ def test_fp32_path_rollout_tracks_fp64_path():
     shift = int((first[0][differ] - first[1][differ]).abs().max()) if bool(differ.any()) else 0
     sa, sb = a.state[:, same_flags], b.state[:, same_flags]
     d = (a.scans[same_flags].double() - b.scans[same_flags].double()).abs()
-    print("[fp32 tolerance] rollout A=1, %d envs x %d steps: %d of %d wall contacts seen one step apart (max shift %d step); "
-          "scans of the other envs: median %.2e m, > 2 cm %.4f %% of beams, max %.3f m" %
+    print("[fp32 tolerance] rollout A=1, %d envs x %d steps: %d of the %d envs with a wall contact saw one of their contacts on another step "
+          "(first contact: max shift %d step); scans of the other envs: median %.2e m, > 2 cm %.4f %% of beams, max %.3f m" %
           (N, T, int(differ.sum()), int(ever.sum()), shift, float(d.median()), 100 * float((d > 2e-2).double().mean()), float(d.max())))
-    assert int(differ.sum()) <= int(ever.sum()) // 20, (int(differ.sum()), int(ever.sum()))
+    assert int(differ.sum()) <= int(ever.sum()) // 10, (int(differ.sum()), int(ever.sum()))
     assert shift <= 1
     assert torch.equal(sa, sb)                             # same flags -> the very same fp64 states (<= 1e-4 rel asked for)
     assert float(d.median()) < 1e-3 and float((d > 2e-2).double().mean()) < 0.02 and float(d.max()) <= 30.0
@@ -388,8 +388,68 @@ def test_step_host_small_batch_paths_agree(dtype, agents):
             assert (np.asarray(got["obs"]).reshape(ref_obs.shape) == ref_obs).all(), t
             assert (np.asarray(got["scans"]) == ref_scans).all(), t
             assert (np.asarray(got["done"]).astype(bool) == ref_done.astype(bool)).all(), t
-    # the mapped path really ran: one more launch per step (k_export_host) than the copy path
-    assert (envs[1].launch_count - launches0[1]) == (envs[2].launch_count - launches0[2]) + T
+    if dtype == "fp64" and agents == 1:
+        # a handful of single-agent fp64 envs: the whole tick, export included, is ONE kernel (k_step_fused64)
+        assert (envs[1].launch_count - launches0[1]) == (envs[2].launch_count - launches0[2]) == T
+    else:
+        # the mapped path really ran: one more launch per step (k_export_host) than the copy path
+        assert (envs[1].launch_count - launches0[1]) == (envs[2].launch_count - launches0[2]) + T
+
+
+@pytest.mark.parametrize("N,yaw", [(1, None), (7, None), (296, None), (40, 0.3)])
+def test_fused_step_is_bit_identical_to_the_three_kernel_step(N, yaw):
+    """Up to F110_FUSED_MAX_ENVS single-agent fp64 envs are stepped by one kernel (k_step_fused64: dynamics -> scan -> iTTC ->
+    lap bookkeeping -> host export); raycast_variant=256 keeps k_dynamics / k_raycast64 / k_finalize.  Same device functions,
+    so everything must be bit-identical: through f110_step, f110_step_host (mapped and pageable buffers), masked resets and
+    auto-resets; berlin has a resolution that is not a power of two, yaw = 0.3 takes the rotated-origin instantiation."""
+    from red_gym_b200 import BatchF110Env
+    import torch
+    rng = np.random.default_rng(N)
+    poses = np.zeros((N, 1, 3))
+    poses[:, 0, :2] = rng.uniform(-0.3, 0.3, (N, 2))
+    poses[:, 0, 2] = rng.uniform(-3, 3, N)
+    if yaw is not None:
+        ox, oy = -11.60654, -26.520793       # berlin.yaml origin
+        c, s_ = np.cos(yaw), np.sin(yaw)
+        dx, dy = poses[..., 0] - ox, poses[..., 1] - oy
+        poses = np.stack([ox + dx * c - dy * s_, oy + dx * s_ + dy * c, poses[..., 2] + yaw], axis=-1)
+    kw = dict(num_envs=N, num_agents=1, map=os.path.join(MAPS, "berlin"), auto_reset=True, reset_poses=poses[: max(1, N // 2)], origin_yaw=yaw)
+    a, b = BatchF110Env(**kw), BatchF110Env(raycast_variant=256, **kw)
+    a.reset(poses); b.reset(poses)
+    assert float(a.scans.min()) < 25.0
+    la, lb = a.launch_count, b.launch_count
+    act_h = torch.zeros((N, 1, 2), dtype=torch.float64).pin_memory()
+    bufs = [dict(obs=torch.zeros((10, N, 1), dtype=torch.float64).pin_memory(), scans=torch.zeros((N, 1, 1080), dtype=torch.float64).pin_memory(),
+                 done=torch.zeros((N,), dtype=torch.uint8).pin_memory()) for _ in range(2)]
+    pag = dict(obs=np.zeros((10, N, 1)), scans=np.zeros((N, 1, 1080)), done=np.zeros((N,), dtype=np.uint8))
+    T = 90
+    for t in range(T):
+        act = np.stack([rng.uniform(-0.4, 0.4, (N, 1)), rng.uniform(0.0, 7.0, (N, 1))], axis=-1)
+        if t % 3 == 0:
+            a.step(act); b.step(act)
+        elif t % 3 == 1:
+            act_h.numpy()[...] = act
+            a.step_host(act_h, bufs[0]["obs"], bufs[0]["scans"], bufs[0]["done"])
+            b.step_host(act_h, bufs[1]["obs"], bufs[1]["scans"], bufs[1]["done"])
+            for k in ("obs", "scans", "done"):
+                assert torch.equal(bufs[0][k], bufs[1][k]), (t, k)
+            assert torch.equal(bufs[0]["scans"].cuda(), a.scans) and torch.equal(bufs[0]["obs"].cuda(), a.obs_block)
+        else:
+            a.step_host(act, pag["obs"], pag["scans"], pag["done"])
+            b.step(act)
+            assert (pag["scans"] == b.scans.cpu().numpy()).all() and (pag["obs"] == b.obs_block.cpu().numpy()).all()
+            assert (pag["done"].astype(bool) == b.done.cpu().numpy().astype(bool)).all()
+        if t == 40 and N > 1:
+            mask = np.arange(N) % 2 == 0
+            a.reset(poses, mask=mask); b.reset(poses, mask=mask)
+        assert torch.equal(a.obs_block, b.obs_block) and torch.equal(a.scans, b.scans), t
+        assert torch.equal(a.done, b.done) and torch.equal(a.toggle_list, b.toggle_list) and torch.equal(a.noise_step, b.noise_step)
+    assert torch.equal(a.episode_count, b.episode_count) and (N < 7 or int(a.episode_count.max()) >= 2)
+    a.count_lookups(True); b.count_lookups(True)
+    a.step(act); b.step(act)
+    assert a.lookups() == b.lookups()
+    # one launch per step against three (four with the host export)
+    assert a.launch_count - la < (b.launch_count - lb) / 2.5
 
 
 def test_sharded_run_is_bit_identical_to_unsharded():

@@ -7,9 +7,11 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from red_gym_b200 import BatchF110Env, MAPS_DIR
 
-for n, yaw in ((1, 1.37079632679), (1, 0.0), (64, 1.37079632679), (64, 0.0), (4096, 1.37079632679), (4096, 0.0)):
+# variant 256: the three-kernel step (k_dynamics / k_raycast64 / k_finalize + k_export_host) instead of k_step_fused64
+for n, yaw, variant in ((1, 1.37079632679, 0), (1, 1.37079632679, 256), (1, 0.0, 0), (64, 1.37079632679, 0), (64, 1.37079632679, 256), (296, 1.37079632679, 0),
+                        (296, 1.37079632679, 256), (4096, 1.37079632679, 0), (4096, 0.0, 0)):
     # yaw == 0 exactly is the yaw of every car stopped by iTTC: the last beam of its scans replays the reference's running index sum
-    env = BatchF110Env(num_envs=n, num_agents=1, map=os.path.join(MAPS_DIR, "example_map"), dtype="fp64", noise="numpy")
+    env = BatchF110Env(num_envs=n, num_agents=1, map=os.path.join(MAPS_DIR, "example_map"), dtype="fp64", noise="numpy", raycast_variant=variant)
     env.reset(np.tile(np.array([[[0.7, 0.0, yaw]]]), (n, 1, 1)))
     act = torch.zeros((n, 1, 2), dtype=torch.float64).pin_memory(); act[..., 1] = 0.0
     obs = torch.zeros((10, n, 1), dtype=torch.float64).pin_memory()
@@ -35,5 +37,5 @@ for n, yaw in ((1, 1.37079632679), (1, 0.0), (64, 1.37079632679), (64, 0.0), (40
         env.step(actd)
     torch.cuda.synchronize()
     dev = (time.perf_counter() - t0) / K * 1e6
-    print("envs %d yaw %g: step_host wall %.1f us | device step back-to-back %.1f us per step | one step GPU (events) %.1f us, ray-cast launch %.1f us"
-          % (n, yaw, wall, dev, float(np.median(gpu)), float(np.median(rc))))
+    print("envs %d yaw %g variant %d: step_host wall %.1f us | device step back-to-back %.1f us per step | one step GPU (events) %.1f us, ray-cast launch %.1f us"
+          % (n, yaw, variant, wall, dev, float(np.median(gpu)), float(np.median(rc))))
