@@ -220,6 +220,13 @@ int f110_last_raycast_ms(f110_sim *sim, float *ms);
  * lookup that misses L1).  out6: stream GB/s, gather sectors/s, ms per stream launch, ms per gather launch, bytes per
  * stream launch, sectors per gather launch.  Synchronous.  (the roof the ray-cast is put against.) */
 int f110_l2_probe(int device, int64_t table_bytes, int32_t repeats, double *out6, void *stream);
+/* Checked build (libf110_b200_checked.so, compiled with -DF110_CHECKED; compute-sanitizer is closed on the B200 pool): every
+ * address / index whose bounds test the fast kernels removed or hoisted is tested, violations are counted per device.
+ * out8: counts since process start -- 0 padded-fp32-map address, 1 fp64 map cell, 2 trig / direction table index, 3 opponent
+ * queue slot, 4 sort bin / slot, 5 beam index, 6 noise row, 7 self-test.  selftest != 0 first commits ONE deliberate violation of
+ * kind 7 (counted only by a checked build: proves the checks are compiled in).  f110_build_is_checked(): 1 / 0. */
+int f110_build_is_checked(void);
+int f110_debug_violations(int device, uint64_t *out8, int32_t selftest);
 /* Number of kernel launches issued by this handle since creation. */
 int64_t f110_launch_count(f110_sim *sim);
 int f110_synchronize(f110_sim *sim, void *stream);

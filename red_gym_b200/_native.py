@@ -7,7 +7,8 @@ import ctypes
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libf110_b200.so")
+# F110_B200_LIB selects another build of the same ABI (the bounds-checked libf110_b200_checked.so of tests/test_gpu_checked_build.py)
+LIB_PATH = os.environ.get("F110_B200_LIB") or os.path.join(HERE, "libf110_b200.so")
 
 F110_ABI_VERSION = 2
 NUM_PARAMS = 18
@@ -24,7 +25,7 @@ SCAN_U16_PER_METRE = 2000.0
 EXPORTS = ["f110_last_error", "f110_abi_version", "f110_device_count", "f110_create", "f110_destroy",
            "f110_set_map", "f110_set_map_image", "f110_edt_build", "f110_set_tables", "f110_set_params", "f110_set_noise_rows", "f110_set_reset_pool",
            "f110_reset", "f110_reset_poses", "f110_step", "f110_step_host", "f110_raycast", "f110_get_buffers", "f110_get_config",
-           "f110_count_lookups", "f110_enable_timing", "f110_last_raycast_ms", "f110_l2_probe", "f110_launch_count", "f110_synchronize",
+           "f110_count_lookups", "f110_enable_timing", "f110_last_raycast_ms", "f110_l2_probe", "f110_build_is_checked", "f110_debug_violations", "f110_launch_count", "f110_synchronize",
            "f110_bitmap_create", "f110_bitmap_destroy", "f110_bitmap_render",
            "f110_pursuit_create", "f110_pursuit_destroy", "f110_pursuit_plan",
            "f110_render_create", "f110_render_destroy", "f110_render_frame",
@@ -103,6 +104,8 @@ def load():
     L.f110_enable_timing.argtypes = [vp, i32]
     L.f110_last_raycast_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_float)]
     L.f110_l2_probe.argtypes = [ctypes.c_int, i64, i32, vp, vp]
+    L.f110_build_is_checked.argtypes = []
+    L.f110_debug_violations.argtypes = [ctypes.c_int, vp, i32]
     L.f110_launch_count.argtypes = [vp]
     L.f110_launch_count.restype = i64
     L.f110_synchronize.argtypes = [vp, vp]

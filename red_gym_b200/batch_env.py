@@ -88,6 +88,7 @@ class BatchF110Env(object):
         self._h = h
         self.device = torch.device("cuda", self.device_index)
         self._noise_rows = 0
+        self._noise_rng = None
         self._steps_since_full_reset = 0
         # setup uploads
         sines, cosines = host.trig_tables(self.theta_dis)
@@ -126,12 +127,18 @@ class BatchF110Env(object):
         self.map = m          # only after the library accepted it: a rejected update leaves the previous map in place
 
     def _ensure_noise(self, rows):
+        """Parity mode: the device table must hold the first `rows` draws of the per-car noise stream (row k = the k-th
+        `default_rng(seed).normal(0, 0.01, B)` after a reset, base_classes.py:202, laser_models.py:451).  PCG64 + ziggurat is
+        a sequential stream: the generator is kept and only the missing rows are drawn (a (count, B) draw fills row by row,
+        the same numbers as count successive B-draws) and uploaded -- one row per step amortised, as in the reference."""
         if self.noise != "numpy" or rows <= self._noise_rows:
             return
         target = max(64, self._noise_rows)
         while target < rows:
             target *= 2
-        new = host.noise_rows(self.seed, self._noise_rows, target - self._noise_rows, self.num_beams)
+        if self._noise_rng is None:
+            self._noise_rng = np.random.default_rng(seed=self.seed)
+        new = self._noise_rng.normal(0., 0.01, size=(target - self._noise_rows, self.num_beams))
         nat.check(self.lib.f110_set_noise_rows(self._h, _hp(np.ascontiguousarray(new)), self._noise_rows, new.shape[0], None))
         self._noise_rows = target
 

@@ -60,6 +60,21 @@ struct f110_sim {
     bool timed = false;            // ev_a / ev_b bracket the ray-cast of the last step
 };
 
+// Per-device violation counters of the checked build (F110_V_*); allocated on first use, shared by every handle of the
+// process, never freed.  The normal build allocates them too (the kernels never write them) so that the ABI is the same.
+static unsigned long long *g_violations[64];
+static unsigned long long *violations_for(int device)
+{
+    if (device < 0 || device >= 64) return nullptr;
+    if (!g_violations[device]) {
+        void *q = nullptr;
+        if (cudaMalloc(&q, 8 * sizeof(unsigned long long)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        cudaMemset(q, 0, 8 * sizeof(unsigned long long));
+        g_violations[device] = (unsigned long long *)q;
+    }
+    return g_violations[device];
+}
+
 template <typename T>
 static int dev_alloc(f110_sim *s, T **p, size_t n, bool zero = true)
 {
@@ -212,6 +227,8 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
         cudaMemset(d.near_start, 1, NA);
     }
     d.actions = s->actions;
+    d.violations = violations_for(device);
+    if (!d.violations) { f110_destroy(s); return fail(F110_ERR_NOMEM, "cudaMalloc failed"); }
     // spatial launch order: pays once more scans are in flight than the GPU holds at a time (and costs 3 small launches)
     s->use_order = NA >= F110_ORDER_FROM && !(cfg->raycast_variant & 64);
     if (s->use_order) {
@@ -898,6 +915,28 @@ extern "C" int f110_l2_probe(int device, int64_t table_bytes, int32_t repeats, d
     cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
     int r = f110_probe_l2(n_sm, (size_t)table_bytes & ~(size_t)127, repeats, out6, (cudaStream_t)stream);
     if (r) return fail(r == 1 ? F110_ERR_NOMEM : F110_ERR_CUDA, "L2 probe failed (%s)", cudaGetErrorString(cudaGetLastError()));
+    return F110_OK;
+}
+
+extern "C" int f110_build_is_checked(void)
+{
+#ifdef F110_CHECKED
+    return 1;
+#else
+    return 0;
+#endif
+}
+
+extern "C" int f110_debug_violations(int device, uint64_t *out8, int32_t selftest)
+{
+    if (!out8) return fail(F110_ERR_INVALID, "null argument");
+    int rc = model_device(device);
+    if (rc) return rc;
+    unsigned long long *v = violations_for(device);
+    if (!v) return fail(F110_ERR_NOMEM, "cudaMalloc failed");
+    if (selftest) f110_launch_check_selftest(v, nullptr);
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(out8, v, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     return F110_OK;
 }
 

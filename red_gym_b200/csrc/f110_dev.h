@@ -35,6 +35,18 @@ static __host__ __device__ __forceinline__ int f110_split_wps(int n, int n_sm)
 #define F110_SPLIT_BELOW64 20480
 #define F110_SPLIT_BELOW32 4608
 
+// Checked build (-DF110_CHECKED -> libf110_b200_checked.so, tests/test_gpu_checked_build.py): compute-sanitizer is closed on
+// the B200 pool, so the code whose speed comes from REMOVED bounds tests (padded fp32 map addressed through a biased base
+// pointer and the mantissa floor; the hoisted map test of the fp64 path; table, queue, bin and beam indices) carries its own:
+// every such address / index is tested and a violation counts into a per-device array that the test reads back
+// (f110_debug_violations).  The normal build compiles the macro to nothing.
+enum { F110_V_EDT32 = 0, F110_V_EDT64 = 1, F110_V_TABLE = 2, F110_V_QUEUE = 3, F110_V_ORDER = 4, F110_V_BEAM = 5, F110_V_NOISE = 6, F110_V_SELFTEST = 7 };
+#ifdef F110_CHECKED
+#define F110_CHECK(viol, cond, code) do { if (!(cond)) atomicAdd((viol) + (code), 1ull); } while (0)
+#else
+#define F110_CHECK(viol, cond, code) do { } while (0)
+#endif
+
 struct F110Dev {
     int n_envs, n_agents, n_beams, integrator, ego_idx, theta_dis;
     int noise_mode, auto_reset, count_lookups, n_pool, scan_is_f32, env_offset;
@@ -90,6 +102,7 @@ struct F110Dev {
     long long noise_rows;
     const double *pool;      // [n_pool][A][3]
     unsigned long long *lookups;
+    unsigned long long *violations;   // [8] per device, F110_V_* (checked build)
     const uint8_t *step_mask;   // [N] or null: envs that take part in this step (masked reset)
     // spatial launch order of the scans (f110_order.cu); order == null: warp w works on agent w
     int *order, *order_key, *order_rank, *order_hist, *order_base;
@@ -116,6 +129,7 @@ void f110_launch_order(const F110Dev &d, cudaStream_t st);      // (chunk, tile,
 void f110_launch_order_poses(const F110Dev &d, const double *poses, int n, int *buf, cudaStream_t st);
 void f110_launch_pad_edt32(const float *src, float *dst, int h, int w, int pad, float oob, cudaStream_t st);
 int f110_probe_l2(int n_sm, size_t table_bytes, int repeats, double *out, cudaStream_t st);      // f110_probe.cu
+void f110_launch_check_selftest(unsigned long long *viol, cudaStream_t st);      // one deliberate violation (F110_V_SELFTEST) in a checked build
 
 // model functions on their own (f110_kernels_fp64.cu, end of file)
 void f110_launch_model_dynamics(const double *x, const double *u, const double *p16, long long n, int ks, double *f, cudaStream_t st);

@@ -238,6 +238,7 @@ static __device__ __forceinline__ double edt_lookup(const F110Dev &d, double x, 
     }
     int c = cell_index<POW2>(xr, d);
     int r = cell_index<POW2>(yr, d);
+    F110_CHECK(d.violations, (unsigned)r < (unsigned)d.map_h && (unsigned)c < (unsigned)d.map_w, F110_V_EDT64);     // the hoisted bounds test must have been right
     return __ldg(d.edt64 + ((unsigned)r * (unsigned)d.map_w + (unsigned)c));
 }
 
@@ -334,6 +335,7 @@ static __device__ __forceinline__ void scan_setup64(const F110Dev &d, double px,
 template <bool ROT, bool POW2, bool COUNT>
 static __device__ __forceinline__ double trace_ray(const F110Dev &d, const Scan64 *c, int ti, unsigned &nlook)
 {
+    F110_CHECK(d.violations, ti >= 0 && ti < d.theta_dis, F110_V_TABLE);
     const double sn = __ldg(d.sines + ti), cs = __ldg(d.cosines + ti);
     // fp32 estimate (conservative through the margin) of the range where the ray nears the border
     const float4 dir = __ldg(d.dir32 + ti);
@@ -387,6 +389,8 @@ static __device__ __forceinline__ void scan_beam(const F110Dev &d, const Scan64 
     int ti = theta_index_of(d, c, i, a);
     double rng = trace_ray<ROT, POW2, COUNT>(d, c, ti, nlook);
     const double *np_ = c->noise;
+    F110_CHECK(d.violations, i >= 0 && i < d.n_beams, F110_V_BEAM);
+    F110_CHECK(d.violations, !np_ || (np_ >= d.noise && np_ + d.n_beams <= d.noise + d.noise_rows * d.n_beams), F110_V_NOISE);
     if (np_) rng += __ldg(np_ + i);
     c->out[i] = rng;
     if (STEP && rng < c->r_gate)
@@ -907,6 +911,7 @@ __global__ void __launch_bounds__(AG_THREADS) k_agents(const F110Dev d)
                     const bool away = !(3.14159265f - fabsf(rel) > cone) && !(fabsf(rp) > 2e-3f);
                     const bool take = inside && (n == 2 ? (away && !towards) : (windows ? towards : (towards || away)));
                     const unsigned m = __ballot_sync(FULL, take);
+                    F110_CHECK(d.violations, !take || (fill + __popc(m & ((1u << lane) - 1u)) < 64 && i >= 0 && i < d.n_beams), F110_V_QUEUE);
                     if (take) queue[wq][fill + __popc(m & ((1u << lane) - 1u))] = (k << 16) | i;
                     fill += __popc(m);
                     __syncwarp();
@@ -987,6 +992,12 @@ __global__ void __launch_bounds__(128) k_finalize(const F110Dev d)
     int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e < d.n_envs) finalize_env(d, e);
 }
+
+__global__ void k_check_selftest(unsigned long long *viol)
+{
+    F110_CHECK(viol, threadIdx.x != 0, F110_V_SELFTEST);      // one deliberate violation: proves the checks are compiled in and read back
+}
+void f110_launch_check_selftest(unsigned long long *viol, cudaStream_t st) { k_check_selftest<<<1, 32, 0, st>>>(viol); }
 
 void f110_launch_finalize(const F110Dev &d, cudaStream_t st)
 {

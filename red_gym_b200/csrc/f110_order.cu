@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(256) k_order_count(const F110Dev d, const doub
     int hb = __float2int_rd((float)yaw * 1.2732395447351628f) & 7;        // 8 / (2 pi)
     int chunk = (ia / agents) / chunk_envs;
     int key = ((chunk * d.order_ty + ty) * d.order_tx + tx) * 8 + hb;
+    F110_CHECK(d.violations, key >= 0 && key < d.order_bins, F110_V_ORDER);
     keys[ia] = key;
     // warp-aggregated: neighbours in env order are often neighbours on the track (same bin); one atomic per distinct key
     const unsigned lane = threadIdx.x & 31;
@@ -113,10 +114,11 @@ static void launch_order_scan(int chunks, int *hist, int *base, int n, int agent
 }
 
 __global__ void __launch_bounds__(256) k_order_scatter(const int *__restrict__ base, const int *__restrict__ keys,
-                                                       const int *__restrict__ ranks, int *__restrict__ order, int n)
+                                                       const int *__restrict__ ranks, int *__restrict__ order, int n, unsigned long long *viol)
 {
     int ia = blockIdx.x * blockDim.x + threadIdx.x;
     if (ia >= n) return;
+    F110_CHECK(viol, base[keys[ia]] + ranks[ia] >= 0 && base[keys[ia]] + ranks[ia] < n, F110_V_ORDER);
     order[base[keys[ia]] + ranks[ia]] = ia;
 }
 
@@ -127,7 +129,7 @@ void f110_launch_order(const F110Dev &d, cudaStream_t st)
                                                     d.order_chunk_envs, d.order_key, d.order_rank);
     const int chunks = (d.n_envs + d.order_chunk_envs - 1) / d.order_chunk_envs;
     launch_order_scan(chunks, d.order_hist, d.order_base, d.order_tx * d.order_ty * 8, d.order_chunk_envs * d.n_agents, st);
-    k_order_scatter<<<(NA + 255) / 256, 256, 0, st>>>(d.order_base, d.order_key, d.order_rank, d.order, NA);
+    k_order_scatter<<<(NA + 255) / 256, 256, 0, st>>>(d.order_base, d.order_key, d.order_rank, d.order, NA, d.violations);
 }
 
 // order of n stand-alone poses (f110_raycast): one chunk; buf = order | key | rank, n each
@@ -136,5 +138,5 @@ void f110_launch_order_poses(const F110Dev &d, const double *poses, int n, int *
     int *order = buf, *keys = buf + n, *ranks = buf + 2 * (size_t)n;
     k_order_count<<<(n + 255) / 256, 256, 0, st>>>(d, poses, poses + 1, poses + 2, 3, n, 1, n, keys, ranks);
     launch_order_scan(1, d.order_hist, d.order_base, d.order_tx * d.order_ty * 8, 0, st);
-    k_order_scatter<<<(n + 255) / 256, 256, 0, st>>>(d.order_base, keys, ranks, order, n);
+    k_order_scatter<<<(n + 255) / 256, 256, 0, st>>>(d.order_base, keys, ranks, order, n, d.violations);
 }
