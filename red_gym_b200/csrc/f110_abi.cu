@@ -150,6 +150,7 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
     d.ego_idx = cfg->ego_idx; d.theta_dis = cfg->theta_dis; d.noise_mode = cfg->noise_mode; d.auto_reset = cfg->auto_reset;
     d.scan_is_f32 = cfg->precision == F110_PRECISION_FP32;
     d.scan_u16 = cfg->scan_format == F110_SCAN_U16;
+    d.no_steal = (cfg->raycast_variant & 512) != 0;
     d.env_offset = cfg->env_offset;
     d.timestep = cfg->timestep; d.fov = cfg->fov; d.eps = cfg->eps; d.max_range = cfg->max_range;
     d.ttc_thresh = cfg->ttc_thresh; d.noise_std = cfg->noise_std; d.seed = cfg->seed;

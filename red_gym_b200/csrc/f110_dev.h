@@ -52,7 +52,7 @@ struct F110Dev {
     int noise_mode, auto_reset, count_lookups, n_pool, scan_is_f32, env_offset;
     int n_sm;                          // SMs of the device (split-scan CTA -> scan mapping)
     unsigned theta_band;               // fp64 beam index: replay the reference's running sum within this many 2^-30 of an integer
-    int scan_u16, pad1_;               // F110_SCAN_U16: scans stored as uint16 at 0.5 mm per LSB (fp32 path, one agent per env)
+    int scan_u16, no_steal;            // no_steal (variant bit 9): warps of a split CTA stay on their own scan;  F110_SCAN_U16: scans stored as uint16 at 0.5 mm per LSB (fp32 path, one agent per env)
     double timestep, fov, eps, max_range, theta_inc, ttc_thresh, noise_std;
     unsigned long long seed;
     unsigned long long inc_fix;        // theta_inc in 32.32 fixed point; kstep = 32 * inc_fix (one round of 32 beams)

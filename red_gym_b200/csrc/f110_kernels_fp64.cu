@@ -489,7 +489,8 @@ __global__ void __launch_bounds__(256, MINB) k_raycast64(const F110Dev d, int en
     if (SPLIT) {
         // own scan first; a warp whose scan has no rounds left takes rounds of the CTA's other scans (scans differ by 2 x in
         // their number of lookups, and the CTA ends with its slowest one).  Which warp casts a round changes no result.
-        for (int k = 0; k < per_cta; k++) {
+        const int n_steal = d.no_steal ? 1 : per_cta;
+        for (int k = 0; k < n_steal; k++) {
             int s2 = slot + k;
             if (s2 >= per_cta) s2 -= per_cta;
             if (row_ia[s2] < 0) continue;
