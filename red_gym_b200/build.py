@@ -37,7 +37,7 @@ def nvcc():
 
 def sources():
     out = [os.path.join(CSRC, u) for u, _ in UNITS]
-    out += [os.path.join(CSRC, "f110_dev.h"), os.path.join(CSRC, "f110_bitmap_dev.h"), os.path.join(CSRC, "f110_pursuit_dev.h"), os.path.join(CSRC, "f110_render_dev.h"), os.path.join(os.path.dirname(HERE), "include", "f110_b200.h")]
+    out += [os.path.join(CSRC, "f110_dev.h"), os.path.join(CSRC, "f110_bitmap_dev.h"), os.path.join(CSRC, "f110_pursuit_dev.h"), os.path.join(CSRC, "f110_render_dev.h"), os.path.join(CSRC, "f110_scan32_dev.h"), os.path.join(os.path.dirname(HERE), "include", "f110_b200.h")]
     return out
 
 

@@ -234,6 +234,10 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
     s->use_order = NA >= F110_ORDER_FROM && !(cfg->raycast_variant & 64);
     if (s->use_order) {
         if (dev_alloc(s, &s->order_buf, 3 * NA)) { f110_destroy(s); return F110_ERR_NOMEM; }
+        // fp32 path: the sort also prepares the scans (32-byte records; variant bit 14 keeps the preparation in the ray-cast)
+        if (d.scan_is_f32 && !(cfg->raycast_variant & 16384)) {
+            if (dev_alloc(s, &d.rec32, 2 * NA, false) || dev_alloc(s, &d.rec32_tmp, 2 * NA, false)) { f110_destroy(s); return F110_ERR_NOMEM; }
+        }
         d.order_chunk_envs = (A == 1 && N >= 8192) ? (int)((N + 7) / 8) : (int)N;   // same chunks as f110_step_host
     }
     cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking);

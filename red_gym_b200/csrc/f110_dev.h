@@ -106,6 +106,7 @@ struct F110Dev {
     const uint8_t *step_mask;   // [N] or null: envs that take part in this step (masked reset)
     // spatial launch order of the scans (f110_order.cu); order == null: warp w works on agent w
     int *order, *order_key, *order_rank, *order_hist, *order_base;
+    float4 *rec32, *rec32_tmp;          // fp32 path: 32-byte scan records prepared by the sort, in launch order / in agent order (f110_scan32_dev.h)
     int order_bins, order_tx, order_ty, order_chunk_envs;
     float order_inv_tile;
 };

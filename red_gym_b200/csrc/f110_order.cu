@@ -13,15 +13,21 @@
 // its own rows, so results are bit-identical to the unordered launch (tests/test_gpu_step.py).
 #include <cuda_runtime.h>
 #include "f110_dev.h"
+#include "f110_scan32_dev.h"
 
 // poses are read as x[i * stride], y[i * stride], yaw[i * stride]: the SoA state of a handle (stride 1) or an
 // (n, 3) pose array handed to f110_raycast (stride 3)
 __global__ void __launch_bounds__(256) k_order_count(const F110Dev d, const double *__restrict__ x, const double *__restrict__ y,
                                                      const double *__restrict__ yawp, int stride, int n, int agents, int chunk_envs,
-                                                     int *__restrict__ keys, int *__restrict__ ranks)
+                                                     int *__restrict__ keys, int *__restrict__ ranks, float4 *__restrict__ rec_tmp)
 {
     int ia = blockIdx.x * blockDim.x + threadIdx.x;
     if (ia >= n) return;
+    if (rec_tmp) {      // fp32 env launch: prepare the scan here, one thread per agent, instead of 8 threads per CTA of the ray-cast
+        ScanJob j;
+        prepare_env_scan<false>(d, ia, j);
+        scan_rec_store(rec_tmp + 2 * (size_t)ia, j);
+    }
     double px = x[(size_t)ia * stride], py = y[(size_t)ia * stride], yaw = yawp[(size_t)ia * stride];
     double xt = px - d.ox, yt = py - d.oy;
     float gx = (float)((xt * d.oc + yt * d.os) * d.inv_res);
@@ -114,29 +120,36 @@ static void launch_order_scan(int chunks, int *hist, int *base, int n, int agent
 }
 
 __global__ void __launch_bounds__(256) k_order_scatter(const int *__restrict__ base, const int *__restrict__ keys,
-                                                       const int *__restrict__ ranks, int *__restrict__ order, int n, unsigned long long *viol)
+                                                       const int *__restrict__ ranks, int *__restrict__ order, int n, unsigned long long *viol,
+                                                       const float4 *__restrict__ rec_tmp, float4 *__restrict__ rec)
 {
     int ia = blockIdx.x * blockDim.x + threadIdx.x;
     if (ia >= n) return;
-    F110_CHECK(viol, base[keys[ia]] + ranks[ia] >= 0 && base[keys[ia]] + ranks[ia] < n, F110_V_ORDER);
-    order[base[keys[ia]] + ranks[ia]] = ia;
+    const int slot = base[keys[ia]] + ranks[ia];
+    F110_CHECK(viol, slot >= 0 && slot < n, F110_V_ORDER);
+    order[slot] = ia;
+    if (rec) {          // the scan records move with the agents: the ray-cast reads them in launch order
+        rec[2 * (size_t)slot] = rec_tmp[2 * (size_t)ia];
+        rec[2 * (size_t)slot + 1] = rec_tmp[2 * (size_t)ia + 1];
+    }
 }
 
 void f110_launch_order(const F110Dev &d, cudaStream_t st)
 {
     const int NA = d.n_envs * d.n_agents;
     k_order_count<<<(NA + 255) / 256, 256, 0, st>>>(d, d.state, d.state + NA, d.state + 4 * (size_t)NA, 1, NA, d.n_agents,
-                                                    d.order_chunk_envs, d.order_key, d.order_rank);
+                                                    d.order_chunk_envs, d.order_key, d.order_rank, d.rec32 ? d.rec32_tmp : nullptr);
     const int chunks = (d.n_envs + d.order_chunk_envs - 1) / d.order_chunk_envs;
     launch_order_scan(chunks, d.order_hist, d.order_base, d.order_tx * d.order_ty * 8, d.order_chunk_envs * d.n_agents, st);
-    k_order_scatter<<<(NA + 255) / 256, 256, 0, st>>>(d.order_base, d.order_key, d.order_rank, d.order, NA, d.violations);
+    k_order_scatter<<<(NA + 255) / 256, 256, 0, st>>>(d.order_base, d.order_key, d.order_rank, d.order, NA, d.violations,
+                                                      d.rec32 ? d.rec32_tmp : nullptr, d.rec32);
 }
 
 // order of n stand-alone poses (f110_raycast): one chunk; buf = order | key | rank, n each
 void f110_launch_order_poses(const F110Dev &d, const double *poses, int n, int *buf, cudaStream_t st)
 {
     int *order = buf, *keys = buf + n, *ranks = buf + 2 * (size_t)n;
-    k_order_count<<<(n + 255) / 256, 256, 0, st>>>(d, poses, poses + 1, poses + 2, 3, n, 1, n, keys, ranks);
+    k_order_count<<<(n + 255) / 256, 256, 0, st>>>(d, poses, poses + 1, poses + 2, 3, n, 1, n, keys, ranks, nullptr);
     launch_order_scan(1, d.order_hist, d.order_base, d.order_tx * d.order_ty * 8, 0, st);
-    k_order_scatter<<<(n + 255) / 256, 256, 0, st>>>(d.order_base, keys, ranks, order, n, d.violations);
+    k_order_scatter<<<(n + 255) / 256, 256, 0, st>>>(d.order_base, keys, ranks, order, n, d.violations, nullptr, nullptr);
 }
