@@ -106,7 +106,7 @@ def run(agents=1, seconds=12.0, solo_seconds=4.0, procs=0, maps_dir=None):
     agent-steps/s of all processes running at once, the single-process figure, core count and CPU model."""
     maps_dir = maps_dir or os.path.join(os.path.dirname(HERE), "red_gym_b200", "maps")      # same example_map.png/.yaml bytes as the reference's examples/
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    procs = procs or cores
+    procs = procs or int(os.environ.get("F110_REF_PROCS", "0")) or cores
     ctx = mp.get_context("spawn")
     ready, go_solo, go_all = ctx.Barrier(procs), ctx.Barrier(procs), ctx.Barrier(procs)
     q = ctx.Queue()

@@ -283,3 +283,46 @@ def test_fp32_philox_noise_is_gaussian_and_independent():
     other.reset(poses)
     assert torch.equal(again.scans, first_scans)
     assert not torch.allclose(other.scans, first_scans, atol=1e-4)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_maps_fp64_bit_exact_fp32_within_tolerance(seed):
+    """Fuzz over what the bundled maps do not vary: random occupancy images (walls + boxes), sizes smaller and larger than
+    max_range, resolutions that are and are not powers of two, arbitrary origins INCLUDING a yaw, odd beam counts and fields of
+    view, poses in free space, on obstacles and outside the map.  fp64: bit-exact against the oracle with the same number of
+    lookups, through the warp-per-scan and the CTA-per-scan kernel; fp32: its own tolerance."""
+    from scipy.ndimage import distance_transform_edt
+    from red_gym_b200 import BatchF110Env, host
+    rng = np.random.default_rng(100 + seed)
+    H, W = int(rng.integers(120, 900)), int(rng.integers(120, 900))
+    res = float(rng.choice([0.05, 0.0625, 0.0437, 0.1, 0.03125, 0.071]))
+    free = np.ones((H, W), dtype=bool)
+    free[:2, :] = free[-2:, :] = free[:, :2] = free[:, -2:] = False
+    for _ in range(int(rng.integers(5, 40))):
+        r0, c0 = int(rng.integers(0, H - 4)), int(rng.integers(0, W - 4))
+        free[r0:r0 + int(rng.integers(1, 30)), c0:c0 + int(rng.integers(1, 30))] = False
+    origin = (float(rng.uniform(-50, 50)), float(rng.uniform(-50, 50)), float(rng.choice([0.0, 0.0, rng.uniform(-3.1, 3.1)])))
+    beams = int(rng.choice([270, 541, 1080, 1081]))
+    fov = float(rng.choice([2 * np.pi, 4.7, 3.0]))
+    edt = res * distance_transform_edt(free)
+    m = host.MapData.from_arrays(edt, res, origin)
+    md = {"dt": m.edt, "h": H, "w": W, "res": res, "ox": origin[0], "oy": origin[1], "oc": m.orig_c, "os": m.orig_s}
+    n = 6000
+    poses = host.free_space_poses(m, n, seed=seed, clearance=0.0)
+    poses[:, 2] = rng.uniform(-10, 10, n)
+    poses[:40, :2] += rng.uniform(-30, 30, (40, 2))            # some of them outside the map / on obstacles
+    ora = fo.OracleEnv(1, 1, map_data=md, noise=False, num_beams=beams, fov=fov)
+    want, lk = ora.scan(poses, return_lookups=True)
+    env = BatchF110Env(num_envs=1, num_agents=1, dtype="fp64", noise="off", num_beams=beams, fov=fov, map_data=m)
+    env.count_lookups(True)
+    got = env.raycast(poses).cpu().numpy()
+    assert (got == want).all(), (seed, H, W, res, origin, beams, fov, np.abs(got - want).max())
+    assert env.lookups() == int(lk.sum()) - n * (beams - 1)
+    env.count_lookups(False)
+    assert (env.raycast(poses[:300]).cpu().numpy() == want[:300]).all()
+    if (m.edt > 1e-4).any() and res > 1e-4:
+        f32 = BatchF110Env(num_envs=1, num_agents=1, dtype="fp32", noise="off", num_beams=beams, fov=fov, map_data=m)
+        g32 = f32.raycast(poses).cpu().numpy()
+        d = np.abs(g32 - want)
+        assert np.median(d) < 1e-3 and (d > 2e-2).mean() < 0.03 and g32.max() <= 30.0 + 1e-3 and g32.min() >= 0.0
+        assert (f32.raycast(poses[:300]).cpu().numpy() == g32[:300]).all()
