@@ -653,3 +653,34 @@ def test_full_size_config4_matches_small_batches_of_the_same_envs():
         assert torch.equal(e.collision_idx, whole.collision_idx[b:b + c]) and torch.equal(e.toggle_list, whole.toggle_list[b:b + c])
     assert bool(torch.isfinite(whole.scans).all()) and bool((whole.collision_idx >= 0).any())      # GJK did fire somewhere
     assert float(whole.scans.min()) > -0.1 and float(whole.scans.max()) < 30.1
+
+
+@pytest.mark.parametrize("fmt", ["native", "u16"])
+def test_masked_reset_in_sorted_fp32_launches(fmt):
+    """>= 32768 fp32 envs: the spatial sort prepares the scans (32-byte records in launch order, f110_scan32_dev.h) and the
+    ray-cast starts from them; raycast_variant=64 turns the sort off and keeps the preparation inside the ray-cast.  A masked
+    reset must leave the unmasked envs untouched and both paths bit-identical, also in the uint16 scan format."""
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    import torch
+    N = 36000
+    kw = dict(num_envs=N, num_agents=1, map=os.path.join(MAPS, "example_map"), dtype="fp32", noise="philox", scan_format=fmt)
+    a, b = BatchF110Env(**kw), BatchF110Env(raycast_variant=64, **kw)
+    rng = np.random.default_rng(2)
+    poses = raceline_poses(N)[rng.permutation(N)][:, None, :]
+    a.reset(poses); b.reset(poses)
+    g = torch.Generator(device="cuda").manual_seed(8)
+    for t in range(60):
+        act = torch.rand((N, 1, 2), generator=g, device="cuda", dtype=torch.float64)
+        act[..., 0] = (act[..., 0] * 2 - 1) * 0.4189
+        act[..., 1] = act[..., 1] * 8.0
+        a.step(act); b.step(act)
+        if t == 30:
+            keep_state, keep_scans = a.obs_block.clone(), a.scans.clone()
+            mask = rng.random(N) < 0.3
+            a.reset(poses, mask=mask); b.reset(poses, mask=mask)
+            m = torch.from_numpy(mask).cuda()
+            assert torch.equal(a.obs_block[:, ~m], keep_state[:, ~m]) and torch.equal(a.scans[~m], keep_scans[~m])
+            assert bool((a.state[3, m] == 0).all()) and bool((a.current_time[m] == 0.01).all())
+        assert torch.equal(a.obs_block, b.obs_block) and torch.equal(a.scans, b.scans) and torch.equal(a.done, b.done), t
+    assert bool(a.collisions.any())
