@@ -676,11 +676,12 @@ def test_masked_reset_in_sorted_fp32_launches(fmt):
         act[..., 1] = act[..., 1] * 8.0
         a.step(act); b.step(act)
         if t == 30:
-            keep_state, keep_scans = a.obs_block.clone(), a.scans.clone()
+            sc = (lambda e: e.scans.view(torch.int16)) if fmt == "u16" else (lambda e: e.scans)     # torch cannot index uint16 on CUDA
+            keep_state, keep_scans = a.obs_block.clone(), sc(a).clone()
             mask = rng.random(N) < 0.3
             a.reset(poses, mask=mask); b.reset(poses, mask=mask)
             m = torch.from_numpy(mask).cuda()
-            assert torch.equal(a.obs_block[:, ~m], keep_state[:, ~m]) and torch.equal(a.scans[~m], keep_scans[~m])
+            assert torch.equal(a.obs_block[:, ~m], keep_state[:, ~m]) and torch.equal(sc(a)[~m], keep_scans[~m])
             assert bool((a.state[3, m] == 0).all()) and bool((a.current_time[m] == 0.01).all())
         assert torch.equal(a.obs_block, b.obs_block) and torch.equal(a.scans, b.scans) and torch.equal(a.done, b.done), t
     assert bool(a.collisions.any())
