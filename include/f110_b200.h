@@ -134,6 +134,17 @@ int f110_set_map_image(f110_sim *sim, const uint8_t *free_px, int32_t h, int32_t
                        double origin_x, double origin_y, double origin_c, double origin_s, void *stream);
 /* get_dt alone, device to device: free_dev DEVICE [h][w] bytes -> edt_dev DEVICE [h][w] doubles (metres). */
 int f110_edt_build(const uint8_t *free_dev, int32_t h, int32_t w, double resolution, double *edt_dev, int device, void *stream);
+/* f110_edt_build for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * No counterpart in the reference.  Same inputs, same output bits; the
+ * column-distance scratch that f110_edt_build allocates per call is a fixed static device array inside the library
+ * (F110_EDT_NOALLOC_MAX_CELLS * 4 bytes = 16 MiB on every GPU that loads the library, until exit), so the call allocates
+ * and frees nothing.  Limits: h * w <= F110_EDT_NOALLOC_MAX_CELLS and w <= F110_EDT_NOALLOC_MAX_WIDTH, else F110_ERR_INVALID.
+ * Asynchronous on `stream`.  All calls on a device share the scratch: it keeps the last call's contents (every cell is
+ * rewritten before it is read, nothing needs clearing), and calls that overlap on the GPU (different streams without an
+ * ordering between them) race -- serialise them. */
+#define F110_EDT_NOALLOC_MAX_CELLS (2048 * 2048)
+#define F110_EDT_NOALLOC_MAX_WIDTH 16384
+int f110_edt_build_noalloc(const uint8_t *free_dev, int32_t h, int32_t w, double resolution, double *edt_dev, int device, void *stream);
 
 /* ---- The model functions of the step on their own, batched (what the reference exposes as
  * f110_gym.envs.dynamic_models / collision_models and pins in its unit tests).  All pointers but params16 are DEVICE

@@ -23,7 +23,7 @@ SCAN_U16_PER_METRE = 2000.0
 
 # every symbol include/f110_b200.h declares (tests check the library exports all of them)
 EXPORTS = ["f110_last_error", "f110_abi_version", "f110_device_count", "f110_create", "f110_destroy",
-           "f110_set_map", "f110_set_map_image", "f110_edt_build", "f110_set_tables", "f110_set_params", "f110_set_noise_rows", "f110_set_reset_pool",
+           "f110_set_map", "f110_set_map_image", "f110_edt_build", "f110_edt_build_noalloc", "f110_set_tables", "f110_set_params", "f110_set_noise_rows", "f110_set_reset_pool",
            "f110_reset", "f110_reset_poses", "f110_step", "f110_step_host", "f110_raycast", "f110_get_buffers", "f110_get_config",
            "f110_count_lookups", "f110_enable_timing", "f110_last_raycast_ms", "f110_l2_probe", "f110_build_is_checked", "f110_debug_violations", "f110_launch_count", "f110_synchronize",
            "f110_bitmap_create", "f110_bitmap_destroy", "f110_bitmap_render",
@@ -89,6 +89,7 @@ def load():
     L.f110_set_map.argtypes = [vp, vp, i32, i32, f64, f64, f64, f64, f64, vp]
     L.f110_set_map_image.argtypes = [vp, vp, i32, i32, f64, f64, f64, f64, f64, vp]
     L.f110_edt_build.argtypes = [vp, i32, i32, f64, vp, ctypes.c_int, vp]
+    L.f110_edt_build_noalloc.argtypes = [vp, i32, i32, f64, vp, ctypes.c_int, vp]
     L.f110_set_tables.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     L.f110_set_params.argtypes = [vp, vp, i32, vp]
     L.f110_set_noise_rows.argtypes = [vp, vp, i64, i64, vp]

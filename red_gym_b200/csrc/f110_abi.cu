@@ -463,6 +463,25 @@ static int model_done(const char *what)
     if (e != cudaSuccess) return fail(F110_ERR_CUDA, "%s failed: %s", what, cudaGetErrorString(e));
     return F110_OK;
 }
+// f110_edt_build without any allocation (no counterpart in the reference):
+// the scratch is a fixed static device array in f110_edt.cu.  Asynchronous on `stream`.
+int f110_edt_build_static(const uint8_t *free_px, double *edt, int h, int w, double res, int device, cudaStream_t st,
+                          const char **what, cudaError_t *err);
+extern "C" int f110_edt_build_noalloc(const uint8_t *free_dev, int32_t h, int32_t w, double res, double *edt_dev, int device, void *stream)
+{
+    if (!free_dev || !edt_dev || h < 1 || w < 1 || !(res > 0)) return fail(F110_ERR_INVALID, "bad EDT arguments");
+    if ((int64_t)h * w > F110_EDT_NOALLOC_MAX_CELLS || w > F110_EDT_NOALLOC_MAX_WIDTH)
+        return fail(F110_ERR_INVALID, "f110_edt_build_noalloc: %d x %d cells exceed the static scratch (at most %d cells, width at most %d); "
+                    "use f110_edt_build", h, w, F110_EDT_NOALLOC_MAX_CELLS, F110_EDT_NOALLOC_MAX_WIDTH);
+    int rc = model_device(device);
+    if (rc) return rc;
+    const char *what = "";
+    cudaError_t e = cudaSuccess;
+    if (f110_edt_build_static(free_dev, edt_dev, h, w, res, device, (cudaStream_t)stream, &what, &e))
+        return fail(F110_ERR_CUDA, "f110_edt_build_noalloc: %s failed: %s", what, cudaGetErrorString(e));
+    return F110_OK;
+}
+
 extern "C" int f110_model_dynamics_st(const double *x_dev, const double *u_dev, const double *params16, int64_t n, double *f_dev,
                                       int device, void *stream)
 {

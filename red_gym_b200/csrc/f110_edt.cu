@@ -57,3 +57,55 @@ void f110_launch_edt_build(const uint8_t *free_px, unsigned *scratch_g, double *
     if (smem > 48 * 1024) cudaFuncSetAttribute(k_edt_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k_edt_rows<<<h, 256, smem, st>>>(scratch_g, edt, h, w, res);
 }
+
+// ------------------------------------------------------------------------------------------------
+// f110_edt_build_noalloc: the same two kernels for callers that cannot call cudaMalloc (code under CUDA graph capture,
+// tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+// The column-distance scratch `g` that f110_edt_build allocates per call lives here in a file-scope device array
+// of a fixed, modest size: F110_EDT_NOALLOC_MAX_CELLS unsigned = 16 MiB, held by every GPU that loads the library until exit.
+// Every call on a device shares that array: it keeps the last call's contents (harmless -- k_edt_columns writes every cell
+// of [h][w] before k_edt_rows reads it, nothing has to start at zero) and two calls that overlap on the GPU (different
+// streams, no ordering between them) race on it.
+// In host code `f110_edt_scratch` is a host-side stand-in, not a device address: its device address is asked for once per
+// device, with that device current, by cudaGetSymbolAddress, and that pointer is what the kernels get.
+// ------------------------------------------------------------------------------------------------
+#define F110_EDT_NOALLOC_MAX_CELLS_ (2048 * 2048)      /* == F110_EDT_NOALLOC_MAX_CELLS of include/f110_b200.h */
+#define F110_EDT_NOALLOC_MAX_WIDTH_ 16384              /* k_edt_rows keeps a row of g^2 in shared memory: 64 KB */
+static __device__ __align__(256) unsigned f110_edt_scratch[F110_EDT_NOALLOC_MAX_CELLS_];
+
+#include <mutex>
+static std::mutex g_scratch_mutex;
+static unsigned *g_scratch_ptr[64];       // per device ordinal: device address of f110_edt_scratch there
+
+// 0 = ok; otherwise *what names the CUDA call that failed and *err its code.  The caller has made `device` current.
+// Calls no cudaMalloc / cudaFree / allocating routine.
+int f110_edt_build_static(const uint8_t *free_px, double *edt, int h, int w, double res, int device, cudaStream_t st,
+                          const char **what, cudaError_t *err)
+{
+    *what = ""; *err = cudaSuccess;
+    if (device < 0 || device >= 64 || (long long)h * w > F110_EDT_NOALLOC_MAX_CELLS_ || w > F110_EDT_NOALLOC_MAX_WIDTH_) {
+        *what = "size check"; *err = cudaErrorInvalidValue;
+        return 1;
+    }
+    unsigned *g;
+    {
+        std::lock_guard<std::mutex> lock(g_scratch_mutex);
+        if (!g_scratch_ptr[device]) {      // set-up, once per device, with that device current
+            unsigned *p = nullptr;
+            cudaError_t e = cudaGetSymbolAddress((void **)&p, f110_edt_scratch);
+            if (e != cudaSuccess || !p) { *what = "cudaGetSymbolAddress(f110_edt_scratch)"; *err = e != cudaSuccess ? e : cudaErrorInvalidSymbol; return 1; }
+            g_scratch_ptr[device] = p;
+        }
+        g = g_scratch_ptr[device];
+    }
+    k_edt_columns<<<(w + 127) / 128, 128, 0, st>>>(free_px, g, h, w);
+    const size_t smem = (size_t)w * 4;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_edt_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) { *what = "cudaFuncSetAttribute(k_edt_rows)"; *err = e; return 1; }
+    }
+    k_edt_rows<<<h, 256, smem, st>>>(g, edt, h, w, res);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { *what = "EDT kernel launch"; *err = e; return 1; }
+    return 0;
+}
