@@ -1,0 +1,104 @@
+"""Edge sizes of the domain on the GPU, against the CPU oracle: many agents per env (up to F110_MAX_AGENTS = 32: 496 GJK pairs
+and 31 opponent casts per agent, collision_idx last-writer-wins), and beam counts that hit every shape of the kernels' beam
+loops -- fewer beams than a warp, exactly one 256-beam block, a block plus a tail, the 65 535-beam maximum."""
+import os
+
+import numpy as np
+import pytest
+
+import f110_oracle as fo
+from conftest import MAPS
+
+pytestmark = pytest.mark.gpu
+REL, SCAN_TOL = 1e-9, 1e-4
+
+
+def _close(a, b, rel=REL):
+    return np.abs(a - b) <= rel * np.maximum(1.0, np.abs(b))
+
+
+@pytest.mark.parametrize("A,N,T", [(8, 64, 40), (32, 6, 10)])
+def test_many_agents_rollout_vs_oracle(A, N, T):
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    rng = np.random.default_rng(A)
+    poses = np.repeat(raceline_poses(N)[:, None, :], A, axis=1)
+    poses[:, 1:, 0] += rng.uniform(-2.5, 2.5, (N, A - 1))
+    poses[:, 1:, 1] += rng.uniform(-2.5, 2.5, (N, A - 1))
+    poses[:, 1:, 2] = rng.uniform(-3, 3, (N, A - 1))
+    kw = dict(map=os.path.join(MAPS, "example_map"), seed=7, ego_idx=A - 1)
+    env = BatchF110Env(num_envs=N, num_agents=A, **kw)
+    ora = fo.OracleEnv(N, A, noise_rows=T + 8, **kw)
+    env.reset(poses); ora.reset(poses)
+    bad = np.zeros(N, dtype=bool)
+    hits = 0
+    for t in range(T + 1):
+        if t > 0:
+            act = np.stack([rng.uniform(-0.3, 0.3, (N, A)), rng.uniform(0.0, 5.0, (N, A))], axis=-1)
+            env.step(act); ora.step(act)
+        st = env.state.permute(1, 2, 0).cpu().numpy()
+        ok = (env.collisions.cpu().numpy() == ora.collisions).all(axis=1) & (env.collision_idx.cpu().numpy() == ora.collision_idx).all(axis=1) & \
+             (env.toggle_list.cpu().numpy() == ora.toggles).all(axis=1) & (env.done.cpu().numpy().astype(bool) == ora.done.astype(bool)) & \
+             _close(st, ora.state).all(axis=(1, 2))
+        # opponent casts: a beam grazing a corner may fall on the other side in the last ulp of sin / cos
+        off = np.abs(env.scans.cpu().numpy() - ora.scans) > SCAN_TOL
+        ok &= off.mean(axis=(1, 2)) < 1e-3
+        bad |= ~ok
+        hits += int((ora.collision_idx >= 0).sum())
+    assert bad.sum() <= (1 if N >= 32 else 0), "envs diverged from the oracle: %s" % np.flatnonzero(bad)
+    assert hits > 0                                     # GJK did fire
+
+
+@pytest.mark.parametrize("B,fov,n", [(2, 4.7, 300), (3, 2 * np.pi, 300), (31, 4.7, 300), (33, 2 * np.pi, 300), (256, 4.7, 300), (65535, 2 * np.pi, 24)])
+def test_raycast_beam_count_edges(B, fov, n):
+    from red_gym_b200 import BatchF110Env
+    ora = fo.OracleEnv(1, 1, map=os.path.join(MAPS, "berlin"), noise=False, num_beams=B, fov=fov)
+    rng = np.random.default_rng(B)
+    poses = np.stack([rng.uniform(-0.4, 0.4, n), rng.uniform(-0.4, 0.4, n), rng.uniform(-7, 7, n)], axis=1)
+    poses[0] = [1e3, -1e3, 0.5]                         # outside the map
+    want = ora.scan(poses)
+    kw = dict(num_envs=1, num_agents=1, map=os.path.join(MAPS, "berlin"), num_beams=B, fov=fov, noise="off")
+    for variant in (0, 128):                            # CTA-per-scan and warp-per-scan kernels
+        got = BatchF110Env(dtype="fp64", raycast_variant=variant, **kw).raycast(poses).cpu().numpy()
+        assert (got == want).all(), (B, variant, np.abs(got - want).max())
+    g32 = [BatchF110Env(dtype="fp32", raycast_variant=v, **kw).raycast(poses).cpu().numpy() for v in (0, 128)]
+    assert (g32[0] == g32[1]).all()
+    d = np.abs(g32[0] - want)
+    assert np.median(d) < 1e-3 and (d > 2e-2).mean() < 0.03
+
+
+@pytest.mark.parametrize("B", [33, 256, 300])
+def test_step_with_other_beam_counts(B):
+    """The whole step at beam counts other than 1080: fp64 against the oracle (iTTC tables, noise rows and the fused /
+    split / whole-scan kernels all depend on B), fp32 CTA-per-scan against warp-per-scan, and the uint16 format."""
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    import torch
+    N, T = 400, 160                                     # long enough for cars that start at rest to reach a wall
+    poses = raceline_poses(N)[:, None, :]
+    kw = dict(map=os.path.join(MAPS, "example_map"), num_beams=B, seed=3)
+    rng = np.random.default_rng(B)
+    acts = np.stack([rng.uniform(-0.4, 0.4, (T, N, 1)), rng.uniform(0.0, 8.0, (T, N, 1))], axis=-1)
+    ora = fo.OracleEnv(N, 1, noise_rows=T + 8, **kw)
+    envs = [BatchF110Env(num_envs=N, num_agents=1, raycast_variant=v, **kw) for v in (0, 128)]
+    f32 = [BatchF110Env(num_envs=N, num_agents=1, dtype="fp32", noise="philox", raycast_variant=v, scan_format=f, **kw)
+           for v, f in ((0, "native"), (128, "native"), (0, "u16" if B % 2 == 0 else "native"))]
+    for e in envs + f32 + [ora]:
+        e.reset(poses)
+    bad = np.zeros(N, dtype=bool)
+    ever = False
+    for t in range(T):
+        for e in envs + f32 + [ora]:
+            e.step(acts[t])
+        ever |= bool(ora.collisions.any())
+        st = envs[0].state.permute(1, 2, 0).cpu().numpy()
+        bad |= ~((envs[0].collisions.cpu().numpy() == ora.collisions).all(axis=1) & _close(st, ora.state).all(axis=(1, 2)) &
+                 (np.abs(envs[0].scans.cpu().numpy() - ora.scans).max(axis=(1, 2)) <= SCAN_TOL))
+    assert bad.sum() <= 1, np.flatnonzero(bad)
+    assert ever or B < 64          # iTTC fired somewhere in the rollout (33 beams, 11 degrees apart, may miss every wall contact)
+    assert torch.equal(envs[0].obs_block, envs[1].obs_block) and torch.equal(envs[0].scans, envs[1].scans)
+    assert torch.equal(f32[0].obs_block, f32[1].obs_block) and torch.equal(f32[0].scans, f32[1].scans)
+    assert torch.equal(f32[0].obs_block, f32[2].obs_block)
+    if B % 2 == 0:
+        q = f32[2].scans.to(torch.int32).double() / 2000.0
+        assert float((q - f32[0].scans.double().clamp(min=0)).abs().max()) <= 0.25e-3 + 2e-6
