@@ -231,7 +231,8 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
     d.violations = violations_for(device);
     if (!d.violations) { f110_destroy(s); return fail(F110_ERR_NOMEM, "cudaMalloc failed"); }
     // spatial launch order: pays once more scans are in flight than the GPU holds at a time (and costs 3 small launches)
-    s->use_order = NA >= F110_ORDER_FROM && !(cfg->raycast_variant & 64);
+    s->use_order = (NA >= (size_t)(d.scan_is_f32 ? F110_ORDER_FROM32 : F110_ORDER_FROM64) || (cfg->raycast_variant & 32768)) &&
+                   !(cfg->raycast_variant & 64);   // bit 15: sort at any size, bit 6: never
     if (s->use_order) {
         if (dev_alloc(s, &s->order_buf, 3 * NA)) { f110_destroy(s); return F110_ERR_NOMEM; }
         // fp32 path: the sort also prepares the scans (32-byte records; variant bit 14 keeps the preparation in the ray-cast)

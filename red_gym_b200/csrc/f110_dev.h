@@ -21,9 +21,13 @@ enum { F110_P_MU, F110_P_CSF, F110_P_CSR, F110_P_LF, F110_P_LR, F110_P_H, F110_P
 // instead of scans n_sm apart.  The grid is n_sm * ceil(n / n_sm) CTAs; the surplus ones exit.
 static __host__ __device__ __forceinline__ int f110_split_grid(int n, int n_sm) { return n_sm * ((n + n_sm - 1) / n_sm); }
 static __device__ __forceinline__ int f110_split_scan(int b, int n, int n_sm) { return (b % n_sm) * ((n + n_sm - 1) / n_sm) + b / n_sm; }
-// Launches of at least this many scans are put in spatial order first (f110_order.cu: three small kernels, ~25 us with
-// their launch gaps).  At 16384 scans that costs what it saves (measured: ray-cast 0.189 -> 0.181 ms, step 0.179 -> 0.200 ms
-// 50 steps after a reset, about break-even once env order has fully decorrelated from track order).
+// Launches of at least this many scans are put in spatial order first (f110_order.cu: three small kernels, ~17-20 us with
+// their launch gaps at these sizes).  Round 2, steady state (env order decorrelated from track order), step time without / with
+// the sort: fp32 8192 envs 0.148 / 0.155 ms, 16384: 0.224 / 0.209, 24576: 0.305 / 0.262; fp64 8192: 0.205 / 0.220,
+// 16384: 0.328 / 0.337, 24576: 0.489 / 0.453 (profiles/r2e_sort_threshold_ab.json).  Hence per precision; variant bit 15 sorts
+// at any size, bit 6 never.  f110_raycast (stand-alone poses) keeps the round-1 threshold.
+#define F110_ORDER_FROM32 16384
+#define F110_ORDER_FROM64 20480
 #define F110_ORDER_FROM 32768
 // warps per scan of a split launch of n scans: 8, 4 or 2, the largest that still makes about one wave of CTAs
 // (8 CTAs of 8 warps per SM), see k_raycast64

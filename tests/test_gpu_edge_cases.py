@@ -102,3 +102,42 @@ def test_step_with_other_beam_counts(B):
     if B % 2 == 0:
         q = f32[2].scans.to(torch.int32).double() / 2000.0
         assert float((q - f32[0].scans.double().clamp(min=0)).abs().max()) <= 0.25e-3 + 2e-6
+
+
+@pytest.mark.parametrize("dtype,N", [("fp32", 16384), ("fp64", 20480)])
+def test_sort_thresholds_per_precision(dtype, N):
+    """The spatial sort starts at F110_ORDER_FROM32 = 16384 (fp32) / F110_ORDER_FROM64 = 20480 (fp64) scans (measured break-even,
+    f110_dev.h): on at exactly that size (three more launches per step than raycast_variant=64), off one scan below, and only a
+    schedule -- step and step_host (8 copy-out chunks of 2048 / 2560 envs, chunk-major order) stay bit-identical."""
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    import torch
+    kw = dict(num_agents=1, map=os.path.join(MAPS, "example_map"), dtype=dtype, noise="philox" if dtype == "fp32" else "numpy",
+              auto_reset=True, reset_poses=raceline_poses(128)[:, None, :])
+    a, b = BatchF110Env(num_envs=N, **kw), BatchF110Env(num_envs=N, raycast_variant=64, **kw)
+    below = BatchF110Env(num_envs=N - 1, **kw)
+    rng = np.random.default_rng(1)
+    poses = raceline_poses(N)[rng.permutation(N)][:, None, :]
+    a.reset(poses); b.reset(poses); below.reset(poses[:N - 1])
+    l0 = (a.launch_count, b.launch_count, below.launch_count)
+    g = torch.Generator(device="cuda").manual_seed(4)
+    sdt = torch.float32 if dtype == "fp32" else torch.float64
+    hb = [dict(obs=torch.zeros((10, N, 1), dtype=torch.float64).pin_memory(), scans=torch.zeros((N, 1, 1080), dtype=sdt).pin_memory(),
+               done=torch.zeros((N,), dtype=torch.uint8).pin_memory()) for _ in range(2)]
+    T = 30
+    for t in range(T):
+        act = torch.rand((N, 1, 2), generator=g, device="cuda", dtype=torch.float64)
+        act[..., 0] = (act[..., 0] * 2 - 1) * 0.4189
+        act[..., 1] = act[..., 1] * 8.0
+        if t % 10 == 9:
+            ah = act.cpu().pin_memory()
+            a.step_host(ah, hb[0]["obs"], hb[0]["scans"], hb[0]["done"]); b.step_host(ah, hb[1]["obs"], hb[1]["scans"], hb[1]["done"])
+            assert all(torch.equal(hb[0][k], hb[1][k]) for k in ("obs", "scans", "done")) and torch.equal(hb[0]["scans"].cuda(), a.scans)
+        else:
+            a.step(act); b.step(act)
+        below.step(act[:N - 1].contiguous())
+        assert torch.equal(a.obs_block, b.obs_block) and torch.equal(a.scans, b.scans), t
+    steps_dev = T - T // 10
+    assert (a.launch_count - l0[0]) - (b.launch_count - l0[1]) == 3 * T          # the three sort kernels, every step
+    assert below.launch_count - l0[2] == 3 * T                                   # one scan below the threshold: no sort
+    assert torch.equal(below.obs_block, a.obs_block[:, :N - 1])                  # ... and the same results
