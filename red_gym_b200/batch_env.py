@@ -313,6 +313,52 @@ class BatchF110Env(object):
                                              ctypes.c_void_p(s[4].data_ptr()), n, ctypes.c_void_p(out.data_ptr()), self._stream()))
         return out
 
+    # ------------------------------------------------------------------ CUDA graphs
+    def reserve_noise(self, steps):
+        """Parity mode (noise='numpy'): upload the noise rows of the next `steps` steps now.  step() does this lazily from
+        Python; a captured graph replays without Python, so the table has to cover every replayed step beforehand."""
+        self._ensure_noise(self._steps_since_full_reset + int(steps) + 1)
+
+    def capture_step_graph(self, actions, steps=1, warmup=3):
+        """One or more steps as a CUDA graph: f110_step enqueues only kernel launches on the caller's stream (no allocation, no
+        synchronisation), so a small-batch step -- tens of microseconds of kernels inside as much Python and launch overhead
+        per call -- can be captured once and replayed with a single launch per replay.
+
+        actions: a CUDA float64 tensor (N, A, 2) -- every captured step reads it, the caller overwrites it in place between
+        replays (e.g. from a policy that is part of a larger captured graph) -- or (steps, N, A, 2): captured step k reads
+        actions[k].  Returns a torch.cuda.CUDAGraph; graph.replay() advances the env by `steps` steps, after which the usual views
+        (self.scans, self.state, self.done, ...) hold the new observation.  `warmup` eager steps are taken first on a side stream
+        (they DO advance the env).  Parity mode: call reserve_noise(total steps to be replayed) first; the episode step counter
+        of this Python object is advanced by replayed(steps) only if the caller says so (note_replayed)."""
+        torch = self._torch
+        if not (isinstance(actions, torch.Tensor) and actions.is_cuda and actions.dtype == torch.float64 and actions.is_contiguous()):
+            raise ValueError("actions must be a contiguous CUDA float64 tensor")
+        per = self._n_act
+        if actions.numel() == per:
+            acts = [actions] * int(steps)
+        elif actions.numel() == per * int(steps):
+            acts = list(actions.reshape(int(steps), self.num_envs, self.num_agents, 2))
+        else:
+            raise ValueError("actions must have shape (num_envs, num_agents, 2) or (steps, num_envs, num_agents, 2)")
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for k in range(int(warmup)):
+                self.step(acts[k % len(acts)])
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        self.reserve_noise(len(acts))
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for a in acts:
+                rc = self._c_step(self._h, a.data_ptr(), self._raw_stream(self.device_index))
+                if rc:
+                    nat.check(rc)
+        return g
+
+    def note_replayed(self, steps):
+        """Tell the Python side that `steps` steps were taken by graph replays (keeps the lazy noise-row upload in step())."""
+        self._steps_since_full_reset += int(steps)
+
     # ------------------------------------------------------------------ extras
     def raycast(self, poses, out=None):
         """ScanSimulator2D.scan(pose, None) for a batch of poses (n, 3) -> (n, num_beams)."""
