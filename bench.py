@@ -299,6 +299,31 @@ def run_b200(args):
                                  "loop_only_warp_inst_per_scan": floor, "frac": floor / prof["warp_inst_per_scan"] * prof["issue_active_pct"] / 100.0,
                                  "thread_inst_per_lookup": prof.get("thread_inst_per_lookup"), "loop_lane_efficiency": prof.get("loop_lane_efficiency")}
 
+    # ---- launch-bound batches: the same steps replayed from a CUDA graph (informational; `value` stays the eager API figure)
+    graph_replay = None
+    if n_envs * agents <= 65536 and not args.no_graph:
+        G = 8
+        gacts = torch.stack(bank[:G])
+        env.reserve_noise(G * (K // G + 8) + 16)
+        cg = env.capture_step_graph(gacts, steps=G, warmup=3)
+        reps = max(1, K // G)
+        for _ in range(2):
+            cg.replay()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(reps):
+            cg.replay()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        env.note_replayed(G * (reps + 2))
+        graph_replay = {"value": float(n_envs) * agents * G * reps * world / (float(t.item()) * 1e-3), "unit": "agent-steps/s",
+                        "ms_per_step": float(t.item()) / (G * reps), "steps_per_graph": G, "replays": reps,
+                        "api": "BatchF110Env.capture_step_graph (torch.cuda.CUDAGraph of f110_step launches)"}
+
     # ---- e2e: the same step through f110_step_host with HOST buffers (H2D actions, D2H observation every step)
     e2e = None
     if not args.no_e2e:
@@ -414,7 +439,7 @@ def run_b200(args):
                            "integrator": "RK4", "noise": noise, "auto_reset": True, "parallelism": "env-shard x%d" % world,
                            "raycast_variant": args.variant, "untimed_steps_before_timing": preroll + W,
                            "l2_flush": L2_FLUSH_NOTE % (scan_gb, 10.24 if dtype == "fp32" else 20.48)},
-                "roofline": roofline, "l2_roofline": l2, "cpu_baseline": cpu_baseline, "e2e": e2e, "strong_scaling": strong,
+                "roofline": roofline, "l2_roofline": l2, "cpu_baseline": cpu_baseline, "e2e": e2e, "graph_replay": graph_replay, "strong_scaling": strong,
                 "collective": collective, "gpu_launches": int(launches), "clocks": clocks}
         print(json.dumps(line))
     if world > 1:
@@ -665,6 +690,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-compact", action="store_true", help="skip the uint16 compact-observation e2e leg")
+    ap.add_argument("--no-graph", action="store_true", help="skip the CUDA-graph replay leg of small workloads")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
