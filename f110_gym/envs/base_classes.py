@@ -92,6 +92,7 @@ class Simulator(object):
         self._batch = None
         self._tables = None
         self._scan_sim = None
+        self._map = None              # (yaml path, image extension) once set_map was called
         self.agents = [RaceCar(self, i) for i in range(num_agents)]
         if map_path is not None:
             self.set_map(map_path, map_ext)
