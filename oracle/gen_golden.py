@@ -397,6 +397,27 @@ def gen_config2_slice():
     print("wrote", out, "envs that hit a wall:", int((coll.max(axis=1) > 0).sum()), "of", n)
 
 
+def gen_rollout_a2_fov():
+    # two agents with a 4.7 rad field of view and the Euler integrator (the other A >= 2 goldens are 2 pi / RK4): the opponent's
+    # corners can lie outside the field of view, where get_blocked_view_indices (laser_models.py:283-315) clamps to the first /
+    # last beam; chaser behind, beside and in front of the leader
+    n, T = 6, 300
+    rng = np.random.default_rng(52)
+    base = np.array([[0.0, 0.0, 1.5], [0.2, 0.1, 1.0], [-0.1, 0.0, 2.0], [0.0, 0.3, -1.2], [0.3, -0.3, 0.4], [0.1, 0.1, 3.0]])
+    rel = np.array([[-1.2, 0.1], [-0.2, 0.5], [1.0, -0.2], [-0.9, -0.4], [0.1, -0.55], [-1.5, 0.0]])      # chaser in the leader's frame
+    poses0 = np.zeros((n, 2, 3))
+    for e in range(n):
+        th = base[e, 2]
+        poses0[e, 0] = base[e]
+        poses0[e, 1] = [base[e, 0] + rel[e, 0] * np.cos(th) - rel[e, 1] * np.sin(th), base[e, 1] + rel[e, 0] * np.sin(th) + rel[e, 1] * np.cos(th),
+                        th + rng.uniform(-0.2, 0.2)]
+    act = np.zeros((T, n, 2, 2))
+    act[..., 0] = rng.uniform(-0.25, 0.25, (T // 12 + 1, n, 2)).repeat(12, axis=0)[:T]
+    act[:, :, 0, 1] = rng.uniform(0.0, 3.0, (T // 12 + 1, n)).repeat(12, axis=0)[:T]
+    act[:, :, 1, 1] = rng.uniform(1.0, 6.0, (T // 12 + 1, n)).repeat(12, axis=0)[:T]
+    _rollout("rollout_a2_euler_fov4p7_skirk", "skirk", 2, "Euler", "4p7", n, T, poses0, act, 100, seed=41)
+
+
 def gen_waypoint_follow():
     """BASELINE config 1: examples/waypoint_follow.py with render() skipped (GL unavailable on this box)."""
     gym = _ref()
@@ -491,6 +512,7 @@ SCENARIOS = {
     "rollout_a3": gen_rollout_a3,
     "rollout_a2_ego1": gen_rollout_a2_ego1,
     "rollout_a2_rot": gen_rollout_a2_rot,
+    "rollout_a2_fov": gen_rollout_a2_fov,
     "rollout_a1_rot": gen_rollout_a1_rot,
     "config2_slice": gen_config2_slice,
     "waypoint_follow": gen_waypoint_follow,
