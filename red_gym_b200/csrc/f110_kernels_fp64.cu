@@ -800,7 +800,9 @@ static __device__ __forceinline__ void agents_cast(const F110Dev &d, const doubl
 }
 
 template <typename SCAN_T>
-__global__ void __launch_bounds__(AG_THREADS) k_agents(const F110Dev d)
+// 8 CTAs of 128 threads per SM (64 registers, 240 bytes of spill): measured on config 4 (131 072 agents) against the compiler's own
+// choice (96 registers, 5 CTAs) and 6 / 10 / 12 CTAs: step 1.887 ms against 1.937 / 1.951 / 1.937 / 1.991 (profiles/r2g_agents_occupancy_ab.json)
+__global__ void __launch_bounds__(AG_THREADS, 8) k_agents(const F110Dev d)
 {
     __shared__ double rec[11][AG_THREADS];      // px, py, yaw, corner x/y * 4 of the current opponent
     __shared__ int span[5][AG_THREADS];         // first / last blocked beam (empty: 1, 0); float bits: bearing offset, cone, edge offset
