@@ -185,7 +185,10 @@ static __device__ __forceinline__ void dynamics_agent(const F110Dev &d, int ia)
     d.pose_pre[2 * (size_t)NA + ia] = x[4];
 }
 
-__global__ void __launch_bounds__(128) k_dynamics(const F110Dev d)
+// 8 CTAs of 128 threads per SM (64 registers, 500 bytes of spill) instead of the compiler's 128 registers / 4 CTAs: round 1 left the
+// spilling version untimed; measured at 2^20 agents the step's non-ray-cast part is 0.298 ms against 0.329 (6 CTAs 0.305, 10 CTAs
+// 0.325; profiles/r2g_dynamics_occupancy_ab.txt) -- the dependent FP64 chain wants resident warps more than registers
+__global__ void __launch_bounds__(128, 8) k_dynamics(const F110Dev d)
 {
     int ia = blockIdx.x * blockDim.x + threadIdx.x;
     if (ia < d.n_envs * d.n_agents) dynamics_agent(d, ia);
