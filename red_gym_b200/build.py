@@ -13,6 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libf110_b200.so")
 LIB_CHECKED = os.path.join(HERE, "libf110_b200_checked.so")      # -DF110_CHECKED: the same code with its own bounds checks (f110_dev.h)
+LIB_PHASES = os.path.join(HERE, "libf110_b200_phases.so")        # -DF110_PHASES: %globaltimer stamps inside k_step_fused64 (tools/phase_probe.py)
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 UNITS = [
@@ -48,18 +49,18 @@ def stale(lib=LIB):
     return any(os.path.getmtime(s) > t for s in sources())
 
 
-def build(force=False, verbose=False, checked=False):
-    LIB = LIB_CHECKED if checked else globals()["LIB"]
+def build(force=False, verbose=False, checked=False, phases=False):
+    LIB = LIB_PHASES if phases else LIB_CHECKED if checked else globals()["LIB"]
     if not force and not stale(LIB):
         return LIB
     cc = nvcc()
-    objdir = os.path.join(HERE, "build_checked" if checked else "build")
+    objdir = os.path.join(HERE, "build_phases" if phases else "build_checked" if checked else "build")
     os.makedirs(objdir, exist_ok=True)
     objs = []
     procs = []
     for unit, extra in UNITS:
         obj = os.path.join(objdir, unit.replace(".cu", ".o"))
-        cmd = [cc] + ARCH + COMMON + extra + (["-DF110_CHECKED"] if checked else []) + (["-Xptxas", "-v"] if verbose else []) + \
+        cmd = [cc] + ARCH + COMMON + extra + (["-DF110_PHASES"] if phases else ["-DF110_CHECKED"] if checked else []) + (["-Xptxas", "-v"] if verbose else []) + \
               ["-c", os.path.join(CSRC, unit), "-o", obj]
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)
@@ -77,4 +78,4 @@ def build(force=False, verbose=False, checked=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, checked="--checked" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, checked="--checked" in sys.argv, phases="--phases" in sys.argv))

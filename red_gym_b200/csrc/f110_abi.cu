@@ -660,14 +660,14 @@ static bool use_fused(const f110_sim *s)
 // kernels of one step, in the order of Simulator.step + F110Env.step.  host_*: mapped host buffers the fused
 // small-batch kernel may write the observation to directly (all null: device buffers only)
 static int enqueue_step(f110_sim *s, const uint8_t *mask_dev, cudaStream_t st, double *host_obs = nullptr, double *host_scans = nullptr,
-                        uint8_t *host_done = nullptr, bool *exported = nullptr)
+                        uint8_t *host_done = nullptr, bool *exported = nullptr, const double *host_cmd = nullptr)
 {
     F110Dev &d = s->d;
     d.step_mask = mask_dev;
     if (exported) *exported = false;
     if (use_fused(s)) {
         if (s->timing) cudaEventRecord(s->ev_a, st);
-        f110_launch_step_fused64(d, host_obs, host_scans, host_done, st);
+        f110_launch_step_fused64(d, host_obs, host_scans, host_done, host_cmd, s->cfg.raycast_variant, st);
         if (s->timing) { cudaEventRecord(s->ev_b, st); s->timed = true; }
         s->launches++;
         d.step_mask = nullptr;
@@ -792,7 +792,8 @@ extern "C" int f110_step_host(f110_sim *s, const double *actions_host, double *o
         if (act_d && (obs_d || !obs_block_host) && (scans_d || !scans_host) && (done_d || !done_host)) {
             s->d.actions = act_d;
             bool exported = false;
-            int rc = enqueue_step(s, nullptr, st, obs_d, (double *)scans_d, done_d, &exported);
+            // host_cmd: a lone env's command travels as a kernel argument (read here, on the host, before the launch)
+            int rc = enqueue_step(s, nullptr, st, obs_d, (double *)scans_d, done_d, &exported, actions_host);
             s->d.actions = s->actions;
             if (rc) return rc;
             if (!exported) {

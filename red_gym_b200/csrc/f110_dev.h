@@ -122,7 +122,8 @@ void f110_launch_raycast32(const F110Dev &d, int env_begin, int env_count, int v
 void f110_launch_agents(const F110Dev &d, cudaStream_t st);      // GJK + opponent ray-cast (A >= 2)
 void f110_launch_finalize(const F110Dev &d, cudaStream_t st);    // collisions, lap bookkeeping, done
 // the whole tick in one kernel (fp64 path, one agent per env, a handful of envs); host pointers: mapped host buffers or null
-void f110_launch_step_fused64(const F110Dev &d, double *obs_host, double *scans_host, uint8_t *done_host, cudaStream_t st);
+void f110_launch_step_fused64(const F110Dev &d, double *obs_host, double *scans_host, uint8_t *done_host, const double *cmd_host, int variant,
+                              cudaStream_t st);
 // launches of at most this many single-agent fp64 envs take the fused kernel (a CTA per env, about one wave at 128 registers)
 #define F110_FUSED_MAX_ENVS 296
 // order: null or a permutation of [0, n): warp w scans pose order[w]

@@ -105,15 +105,17 @@ static __device__ __forceinline__ unsigned pool_index(int e, long long episode, 
 }
 
 // RaceCar.update_pose without the scan (base_classes.py:254-402) for agent ia: steering FIFO, pid, RK4 / Euler, yaw wrap
-static __device__ __forceinline__ void dynamics_agent(const F110Dev &d, int ia)
+// cmd: the agent's (steer, velocity) command when the caller already holds it (the single-env step gets it as a kernel
+// argument instead of reading the caller's host buffer over PCIe), else null -> d.actions
+static __device__ __forceinline__ void dynamics_agent(const F110Dev &d, int ia, const double *cmd = nullptr)
 {
     const int NA = d.n_envs * d.n_agents;
     int e = ia / d.n_agents, a = ia - e * d.n_agents;
     if (d.step_mask && !d.step_mask[e]) return;
 
     double x[7];
-    double raw_steer = d.actions[2 * ia + 0];
-    double vel_cmd = d.actions[2 * ia + 1];
+    double raw_steer = cmd ? cmd[0] : d.actions[2 * ia + 0];
+    double vel_cmd = cmd ? cmd[1] : d.actions[2 * ia + 1];
     int slen = d.steer_len[ia];
     if (d.auto_reset && d.reset_pending[e]) {
         // F110Env.reset on the device: the pending env restarts from a pool pose and this step is
@@ -137,6 +139,11 @@ static __device__ __forceinline__ void dynamics_agent(const F110Dev &d, int ia)
         for (int i = 0; i < 7; i++) x[i] = d.state[(size_t)i * NA + ia];
     }
 
+    // every load of the step before its first store (nothing tells the compiler that the arrays do not alias, and a load
+    // it must keep behind a store is one more trip to L2 on the single-env path, where thread 0 of k_step_fused64 runs this alone)
+    const double *pp = d.params + F110_NP * a;
+    VehP p = { pp[0], pp[1], pp[2], pp[3], pp[4], pp[5], pp[6], pp[7], pp[8], pp[9], pp[10], pp[11], pp[12], pp[13], pp[14], pp[15] };
+
     // steering delay FIFO of depth 2 (base_classes.py:268-276)
     double b0 = d.steer_buf[ia], b1 = d.steer_buf[NA + ia];
     double steer;
@@ -145,9 +152,6 @@ static __device__ __forceinline__ void dynamics_agent(const F110Dev &d, int ia)
     d.steer_buf[NA + ia] = b0;
     d.steer_buf[ia] = raw_steer;
     d.steer_len[ia] = (uint8_t)slen;
-
-    const double *pp = d.params + F110_NP * a;
-    VehP p = { pp[0], pp[1], pp[2], pp[3], pp[4], pp[5], pp[6], pp[7], pp[8], pp[9], pp[10], pp[11], pp[12], pp[13], pp[14], pp[15] };
 
     double sv, accl;
     pid_ctrl(vel_cmd, steer, x[3], x[2], p.sv_max, p.a_max, p.v_max, p.v_min, accl, sv);
@@ -949,35 +953,46 @@ void f110_launch_agents(const F110Dev &d, cudaStream_t st)
 // ------------------------------------------------------------------------------------------------
 // F110Env.step tail: time, _check_done (f110_env.py:202-244, 292-299)
 // ------------------------------------------------------------------------------------------------
+// the lap counter of one agent (f110_env.py:202-244): (dx, dy) = position - start, R = the start frame's rotation
+static __device__ __forceinline__ void lap_update(double r0, double r1, double r2, double r3, double dx, double dy, int &tg, bool &near)
+{
+    double d0 = r0 * dx + r1 * dy;
+    double ty = r2 * dx + r3 * dy;
+    if (ty > 2) ty -= 2;
+    else if (ty < -2) ty = -2 - ty;
+    else ty = 0;
+    double dist2 = d0 * d0 + ty * ty;
+    bool closes = dist2 <= 0.1;
+    if (closes && !near) { near = true; tg += 1; }
+    else if (!closes && near) { near = false; tg += 1; }
+}
+
 static __device__ __forceinline__ void finalize_env(const F110Dev &d, int e)
 {
     if (d.step_mask && !d.step_mask[e]) return;
     const int A = d.n_agents, NA = d.n_envs * A;
-    double t = d.cur_time[e] + d.timestep;
-    d.cur_time[e] = t;
-    d.noise_step[e] += 1;
+    // loads first, stores last (per env and per agent): with the stores in between every load would wait for the one before it
+    const double t = d.cur_time[e] + d.timestep;
+    const long long ns = d.noise_step[e];
     const double *R = d.start_rot + 4 * (size_t)e;
     const double r0 = R[0], r1 = R[1], r2 = R[2], r3 = R[3];
+    const long long episodes = d.auto_reset ? d.episode_count[e] : 0;
+    // collisions of the ego: with several agents k_agents wrote them (GJK | iTTC); alone it is the iTTC flag (base_classes.py:581-582)
+    bool ego_collides = A > 1 && d.collisions[(size_t)e * A + d.ego_idx] != 0.0;
     bool all_done = true;
     for (int a = 0; a < A; a++) {
-        size_t ia = (size_t)e * A + a;
-        if (A == 1) {   // no GJK pass: collisions = iTTC flag (base_classes.py:581-582)
-            d.collisions[ia] = d.in_collision[ia] ? 1.0 : 0.0;
-            d.collision_idx[ia] = -1.0;
-        }
-        double dx = d.state[ia] - d.start_x[ia];
-        double dy = d.state[(size_t)NA + ia] - d.start_y[ia];
-        double d0 = r0 * dx + r1 * dy;
-        double ty = r2 * dx + r3 * dy;
-        if (ty > 2) ty -= 2;
-        else if (ty < -2) ty = -2 - ty;
-        else ty = 0;
-        double dist2 = d0 * d0 + ty * ty;
-        bool closes = dist2 <= 0.1;
+        const size_t ia = (size_t)e * A + a;
+        const bool hit = A == 1 && d.in_collision[ia];
+        const double dx = d.state[ia] - d.start_x[ia];
+        const double dy = d.state[(size_t)NA + ia] - d.start_y[ia];
         int tg = d.toggles[ia];
         bool near = d.near_start[ia] != 0;
-        if (closes && !near) { near = true; tg += 1; }
-        else if (!closes && near) { near = false; tg += 1; }
+        if (A == 1) {
+            d.collisions[ia] = hit ? 1.0 : 0.0;
+            d.collision_idx[ia] = -1.0;
+            ego_collides = hit;
+        }
+        lap_update(r0, r1, r2, r3, dx, dy, tg, near);
         d.near_start[ia] = near ? 1 : 0;
         d.toggles[ia] = tg;
         d.checkpoint_done[ia] = tg >= 4 ? 1 : 0;
@@ -985,11 +1000,13 @@ static __device__ __forceinline__ void finalize_env(const F110Dev &d, int e)
         if (tg < 4) d.lap_times[ia] = t;
         if (tg < 4) all_done = false;
     }
-    bool done = (d.collisions[(size_t)e * A + d.ego_idx] != 0.0) || all_done;
+    d.cur_time[e] = t;
+    d.noise_step[e] = ns + 1;
+    const bool done = ego_collides || all_done;
     d.done[e] = done ? 1 : 0;
     if (d.auto_reset) {
         d.reset_pending[e] = done ? 1 : 0;
-        if (done) d.episode_count[e] += 1;
+        if (done) d.episode_count[e] = episodes + 1;
     }
 }
 
@@ -1014,59 +1031,133 @@ void f110_launch_finalize(const F110Dev &d, cudaStream_t st)
 // The whole tick of a single-agent env in ONE kernel (north_star: "dynamics, integration and TTC fused into one per-env
 // kernel"), for a handful of envs: a CTA per env.  Thread 0 integrates the car (dynamics_agent) and prepares the scan, the
 // eight warps cast it (rounds claimed from a shared counter, as in the split kernel), thread 0 applies the iTTC outcome
-// and the lap bookkeeping (finalize_env), and -- when the caller's host buffers are mapped -- the CTA writes the env's
-// observation straight into them.  Same device functions as k_dynamics / k_raycast64 / k_finalize, so the results are
-// bit-identical to the three-kernel step (tests/test_gpu_step.py); what goes away is three launches and their gaps, which
-// dominate a single-env step (one env: 46 us of kernels in an 80 us call before).
+// and the lap bookkeeping (finalize_env's arithmetic for one agent: lap_update), and -- when the caller's host buffers are
+// mapped -- the CTA writes the env's observation straight into them.  Same device functions as k_dynamics / k_raycast64 /
+// k_finalize, so the results are bit-identical to the three-kernel step (tests/test_gpu_step.py); what goes away is three
+// launches and their gaps, which dominate a single-env step (one env: 46 us of kernels in an 80 us call before).
 // ------------------------------------------------------------------------------------------------
 struct F110HostOut {
     double *obs;            // [10][N] or null
     double *scans;          // [N][B] or null
     uint8_t *done;          // [N] or null
+    double cmd[2];          // one env: its (steer, velocity) command, read by the host (has_cmd) -- saves the kernel a PCIe read
+    int has_cmd;
 };
 
-template <bool ROT, bool POW2, bool COUNT>
-__global__ void __launch_bounds__(256) k_step_fused64(const F110Dev d, const F110HostOut ho)
+// what the step's tail needs from global memory, fetched by a thread of another warp while the scan is cast, so that thread 0's
+// tail is shared-memory reads, arithmetic and stores (0.4 us; tools/phase_probe.py -- the single-env kernel is 8 us of
+// thread 0's RK4, 1 us of scan preparation and 7.5 us until the slowest round of the scan is in)
+struct FusedTail {
+    double x[7];            // the car's state after the dynamics
+    double cur_time, r0, r1, r2, r3, start_x, start_y, lap_time;
+    long long noise_step, episodes;
+    int toggles, near;
+};
+
+#ifdef F110_PHASES      // diagnostic build (build.py --phases, tools/phase_probe.py): clock64 stamps of env 0's step by thread 0
+// [0..7] %globaltimer (ns; read at the first and the last stamp only, for the clock rate), [8..15] clock64 at stamp i.
+// (A stamp placed right after __syncthreads is taken BEFORE the barrier resolves -- BAR.SYNC.DEFER_BLOCKING lets the warp run on
+// to the first instruction that needs the barrier -- hence stamp 4 sits inside thread 0's branch behind it.)
+__device__ unsigned long long f110_phase[16];
+extern "C" int f110_debug_phases(unsigned long long *out16) { return (int)cudaMemcpyFromSymbol(out16, f110_phase, sizeof(f110_phase)); }
+#define PHASE(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) { unsigned long long t_ = 0, c_; if ((i) == 0 || (i) == 6) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_) :: "memory"); asm volatile("mov.u64 %0, %%clock64;" : "=l"(c_) :: "memory"); f110_phase[i] = t_; f110_phase[8 + i] = c_; } } while (0)
+#else
+#define PHASE(i) do { } while (0)
+#endif
+
+// NT threads per CTA: 256, or 1024 when there are no more envs than SMs -- a lone scan is 34 rounds of dependent gathers, and with
+// 32 warps every warp casts about one round instead of four (the 1024-thread build is capped at 64 registers: thread 0's RK4 spills,
+// which costs less than it saves -- see k_dynamics).
+template <bool ROT, bool POW2, bool COUNT, int NT>
+__global__ void __launch_bounds__(NT) k_step_fused64(const F110Dev d, const F110HostOut ho)
 {
     __shared__ Scan64 row;
+    __shared__ FusedTail tail;
     __shared__ int next_round, hit_any, active;
     const int e = (int)blockIdx.x, lane = threadIdx.x & 31;      // one agent per env: ia == e
+    const int N = d.n_envs;
+    PHASE(0);
     if (threadIdx.x == 0) {
         active = !(d.step_mask && !d.step_mask[e]);
         if (active) {
-            dynamics_agent(d, e);
+            dynamics_agent(d, e, ho.has_cmd ? ho.cmd : nullptr);
+            PHASE(1);
             prepare_env_scan64<ROT, POW2>(d, e, &row, true);
         }
         next_round = 0;
         hit_any = 0;
     }
+    PHASE(2);
     __syncthreads();
     if (!active) return;
+    if (threadIdx.x == 32) {      // after the barrier: what dynamics_agent wrote (also an auto-reset's new start frame) is visible
+#pragma unroll
+        for (int k = 0; k < 7; k++) tail.x[k] = d.state[(size_t)k * N + e];
+        const double *R = d.start_rot + 4 * (size_t)e;
+        tail.r0 = R[0]; tail.r1 = R[1]; tail.r2 = R[2]; tail.r3 = R[3];
+        tail.cur_time = d.cur_time[e];
+        tail.noise_step = d.noise_step[e];
+        tail.start_x = d.start_x[e];
+        tail.start_y = d.start_y[e];
+        tail.lap_time = d.lap_times[e];
+        tail.toggles = d.toggles[e];
+        tail.near = d.near_start[e];
+        tail.episodes = d.auto_reset ? d.episode_count[e] : 0;
+    }
     bool hit = false;
     unsigned nlook = 0;
     scan_rounds_claimed<ROT, POW2, true, COUNT>(d, &row, hit, nlook, &next_round, threadIdx.x == 0);
+    PHASE(3);
     if (__any_sync(FULL, hit) && lane == 0) atomicOr(&hit_any, 1);
     __syncthreads();
-    const int N = d.n_envs;
     if (threadIdx.x == 0) {
-        const bool h = hit_any != 0;      // RaceCar.check_ttc (base_classes.py:241-250)
-        if (h) { d.state[3 * (size_t)N + e] = 0.; d.state[4 * (size_t)N + e] = 0.; d.state[5 * (size_t)N + e] = 0.; d.state[6 * (size_t)N + e] = 0.; }
+        PHASE(4);
+        // RaceCar.check_ttc (base_classes.py:241-250), then finalize_env for the env's only agent, from `tail` instead of global memory
+        const bool h = hit_any != 0;
+        double x[7];
+#pragma unroll
+        for (int k = 0; k < 7; k++) x[k] = tail.x[k];
+        if (h) {
+            x[3] = 0.; x[4] = 0.; x[5] = 0.; x[6] = 0.;
+            d.state[3 * (size_t)N + e] = 0.; d.state[4 * (size_t)N + e] = 0.; d.state[5 * (size_t)N + e] = 0.; d.state[6 * (size_t)N + e] = 0.;
+        }
         d.in_collision[e] = h ? 1 : 0;
-        finalize_env(d, e);
-        if (ho.done) ho.done[e] = d.done[e];
+        const double t = tail.cur_time + d.timestep;
+        int tg = tail.toggles;
+        bool near = tail.near != 0;
+        lap_update(tail.r0, tail.r1, tail.r2, tail.r3, x[0] - tail.start_x, x[1] - tail.start_y, tg, near);
+        const double coll = h ? 1.0 : 0.0, laps = (double)(tg / 2), lap_time = tg < 4 ? t : tail.lap_time;
+        const bool done = h || tg >= 4;
+        d.collisions[e] = coll;
+        d.collision_idx[e] = -1.0;
+        d.near_start[e] = near ? 1 : 0;
+        d.toggles[e] = tg;
+        d.checkpoint_done[e] = tg >= 4 ? 1 : 0;
+        d.lap_counts[e] = laps;
+        if (tg < 4) d.lap_times[e] = t;
+        d.cur_time[e] = t;
+        d.noise_step[e] = tail.noise_step + 1;
+        d.done[e] = done ? 1 : 0;
+        if (d.auto_reset) {
+            d.reset_pending[e] = done ? 1 : 0;
+            if (done) d.episode_count[e] = tail.episodes + 1;
+        }
+        if (ho.done) ho.done[e] = done ? 1 : 0;
         if (ho.obs) {
 #pragma unroll
-            for (int k = 0; k < 7; k++) ho.obs[(size_t)k * N + e] = d.state[(size_t)k * N + e];
-            ho.obs[7 * (size_t)N + e] = d.collisions[e];
-            ho.obs[8 * (size_t)N + e] = d.lap_times[e];
-            ho.obs[9 * (size_t)N + e] = d.lap_counts[e];
+            for (int k = 0; k < 7; k++) ho.obs[(size_t)k * N + e] = x[k];
+            ho.obs[7 * (size_t)N + e] = coll;
+            ho.obs[8 * (size_t)N + e] = lap_time;
+            ho.obs[9 * (size_t)N + e] = laps;
         }
+        PHASE(5);
     }
     if (ho.scans) {       // the scan this CTA just wrote (visible CTA-wide after the barrier) -> the caller's host buffer
         const double *src = (const double *)d.scans + (size_t)e * d.n_beams;
         double *dst = ho.scans + (size_t)e * d.n_beams;
-        for (int i = threadIdx.x; i < d.n_beams; i += 256) dst[i] = src[i];
+        for (int i = threadIdx.x; i < d.n_beams; i += NT) dst[i] = src[i];
     }
+    PHASE(6);
     if (COUNT) {
 #pragma unroll
         for (int o = 16; o; o >>= 1) nlook += __shfl_xor_sync(FULL, nlook, o);
@@ -1074,14 +1165,18 @@ __global__ void __launch_bounds__(256) k_step_fused64(const F110Dev d, const F11
     }
 }
 
-void f110_launch_step_fused64(const F110Dev &d, double *obs_host, double *scans_host, uint8_t *done_host, cudaStream_t st)
+void f110_launch_step_fused64(const F110Dev &d, double *obs_host, double *scans_host, uint8_t *done_host, const double *cmd_host, int variant,
+                              cudaStream_t st)
 {
-    F110HostOut ho = { obs_host, scans_host, done_host };
+    F110HostOut ho = { obs_host, scans_host, done_host, { 0., 0. }, 0 };
+    if (cmd_host && d.n_envs == 1) { ho.cmd[0] = cmd_host[0]; ho.cmd[1] = cmd_host[1]; ho.has_cmd = 1; }
     const bool cnt = d.count_lookups != 0;
+    const bool wide = d.n_envs <= d.n_sm && !(variant & 1);        // variant bit 0: always 256 threads per env
 #define FUSED(R, P)                                                                   \
     do {                                                                              \
-        if (cnt) k_step_fused64<R, P, true><<<d.n_envs, 256, 0, st>>>(d, ho);         \
-        else k_step_fused64<R, P, false><<<d.n_envs, 256, 0, st>>>(d, ho);            \
+        if (cnt) k_step_fused64<R, P, true, 256><<<d.n_envs, 256, 0, st>>>(d, ho);    \
+        else if (wide) k_step_fused64<R, P, false, 1024><<<d.n_envs, 1024, 0, st>>>(d, ho); \
+        else k_step_fused64<R, P, false, 256><<<d.n_envs, 256, 0, st>>>(d, ho);       \
     } while (0)
     if (d.has_rot) FUSED(true, false);
     else if (d.res_pow2) FUSED(false, true);
