@@ -183,7 +183,10 @@ int f110_set_tables(f110_sim *sim, const double *sines, const double *cosines, c
 int f110_set_params(f110_sim *sim, const double *params18, int32_t agent_idx, void *stream);
 
 /* F110_NOISE_TABLE: upload rows [first_row, first_row+n_rows) of the host noise stream
- * (n_beams doubles each).  The table must cover max(noise_step)+1 before each step. */
+ * (n_beams doubles each).  The table must cover max(noise_step)+1 before each step.
+ * Rows appended behind the table's end (first_row >= rows uploaded so far) travel on an internal stream and
+ * `stream` is made to wait for them: steps already enqueued on `stream` keep running meanwhile.  Rows that
+ * overwrite existing ones, and a table that has to grow, synchronise `stream`.  `rows` is free on return. */
 int f110_set_noise_rows(f110_sim *sim, const double *rows, int64_t first_row, int64_t n_rows, void *stream);
 
 /* Pool of start poses for auto_reset: [n_poses][n_agents][3] host doubles. */

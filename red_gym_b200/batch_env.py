@@ -126,20 +126,20 @@ class BatchF110Env(object):
                                             m.orig_c, m.orig_s, None))
         self.map = m          # only after the library accepted it: a rejected update leaves the previous map in place
 
-    def _ensure_noise(self, rows):
+    def _ensure_noise(self, rows, exact=False):
         """Parity mode: the device table must hold the first `rows` draws of the per-car noise stream (row k = the k-th
         `default_rng(seed).normal(0, 0.01, B)` after a reset, base_classes.py:202, laser_models.py:451).  PCG64 + ziggurat is
         a sequential stream: the generator is kept and only the missing rows are drawn (a (count, B) draw fills row by row,
-        the same numbers as count successive B-draws) and uploaded -- one row per step amortised, as in the reference."""
+        the same numbers as count successive B-draws) and uploaded -- one row per step amortised, as in the reference.
+        Lazy growth (from step) comes in chunks of 128 rows, 2 ms of numpy each, uploaded beside the step's stream: the steps
+        already queued cover it, where a table that doubled stalled the device for as long as the draw took (75 ms at 4096 rows)."""
         if self.noise != "numpy" or rows <= self._noise_rows:
             return
-        target = max(64, self._noise_rows)
-        while target < rows:
-            target *= 2
+        target = int(rows) if exact else max(int(rows), self._noise_rows + 128)
         if self._noise_rng is None:
             self._noise_rng = np.random.default_rng(seed=self.seed)
         new = self._noise_rng.normal(0., 0.01, size=(target - self._noise_rows, self.num_beams))
-        nat.check(self.lib.f110_set_noise_rows(self._h, _hp(np.ascontiguousarray(new)), self._noise_rows, new.shape[0], None))
+        nat.check(self.lib.f110_set_noise_rows(self._h, _hp(np.ascontiguousarray(new)), self._noise_rows, new.shape[0], self._stream()))
         self._noise_rows = target
 
     def _wrap_buffers(self):
@@ -317,7 +317,7 @@ class BatchF110Env(object):
     def reserve_noise(self, steps):
         """Parity mode (noise='numpy'): upload the noise rows of the next `steps` steps now.  step() does this lazily from
         Python; a captured graph replays without Python, so the table has to cover every replayed step beforehand."""
-        self._ensure_noise(self._steps_since_full_reset + int(steps) + 1)
+        self._ensure_noise(self._steps_since_full_reset + int(steps) + 1, exact=True)
 
     def capture_step_graph(self, actions, steps=1, warmup=3):
         """One or more steps as a CUDA graph: f110_step enqueues only kernel launches on the caller's stream (no allocation, no

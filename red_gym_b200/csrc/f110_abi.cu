@@ -53,6 +53,7 @@ struct f110_sim {
     double *stage_poses = nullptr, *stage_rot = nullptr;
     uint8_t *stage_mask = nullptr;
     cudaStream_t copy_stream = nullptr;
+    cudaEvent_t noise_ev = nullptr;      // end of the last noise-row upload on copy_stream (f110_set_noise_rows)
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;
     std::vector<cudaEvent_t> chunk_ev;
     long long launches = 0;
@@ -265,6 +266,7 @@ extern "C" int f110_destroy(f110_sim *s)
     if (s->noise) cudaFree(s->noise);
     if (s->pool) cudaFree(s->pool);
     for (cudaEvent_t ev : s->chunk_ev) cudaEventDestroy(ev);
+    if (s->noise_ev) cudaEventDestroy(s->noise_ev);
     if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
     if (s->ev_a) cudaEventDestroy(s->ev_a);
     if (s->ev_b) cudaEventDestroy(s->ev_b);
@@ -621,8 +623,18 @@ extern "C" int f110_set_noise_rows(f110_sim *s, const double *rows, int64_t firs
         s->noise = nn; s->noise_cap = cap;
         s->d.noise = nn;
     }
-    CK(cudaMemcpyAsync(s->noise + (size_t)first_row * B, rows, (size_t)n_rows * B * 8, cudaMemcpyHostToDevice, st));
-    CK(cudaStreamSynchronize(st));
+    if (first_row >= s->d.noise_rows) {
+        // rows no enqueued step reads (a step is only launched for rows below noise_rows): upload them beside the caller's
+        // stream instead of draining it -- steps already queued keep the GPU busy, later ones wait for the event
+        if (!s->noise_ev) CK(cudaEventCreateWithFlags(&s->noise_ev, cudaEventDisableTiming));
+        CK(cudaMemcpyAsync(s->noise + (size_t)first_row * B, rows, (size_t)n_rows * B * 8, cudaMemcpyHostToDevice, s->copy_stream));
+        CK(cudaEventRecord(s->noise_ev, s->copy_stream));
+        CK(cudaStreamWaitEvent(st, s->noise_ev, 0));
+        CK(cudaStreamSynchronize(s->copy_stream));      // the caller's buffer is free again on return
+    } else {
+        CK(cudaMemcpyAsync(s->noise + (size_t)first_row * B, rows, (size_t)n_rows * B * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+    }
     if (need > s->d.noise_rows) s->d.noise_rows = need;
     return F110_OK;
 }

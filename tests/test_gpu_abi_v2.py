@@ -203,3 +203,31 @@ def test_l2_probe_reports_a_bandwidth():
     stream, gather = out[0], out[1]
     assert 1000.0 < stream < 60000.0                       # GB/s
     assert 1e10 < gather < 2e12                            # 32-byte sectors per second
+
+
+def test_noise_rows_grown_lazily_match_rows_reserved_up_front():
+    """Parity mode: step() extends the noise table 128 rows at a time, uploaded beside the stepping stream
+    (f110_set_noise_rows: rows behind the table's end do not drain the caller's stream); the scans must be the ones of an env
+    whose rows were all uploaded before the first step -- across five chunk borders and two table reallocations, on a
+    stream of the caller's own with steps queued up behind each other."""
+    import torch
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    N, T = 600, 700
+    kw = dict(num_envs=N, num_agents=1, map=os.path.join(MAPS, "example_map"), dtype="fp64", noise="numpy", seed=4242)
+    poses = raceline_poses(N)[:, None, :]
+    g = torch.Generator(device="cuda").manual_seed(11)
+    acts = [_actions(torch, N, 1, g) for _ in range(16)]
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        a, b = BatchF110Env(**kw), BatchF110Env(**kw)
+        a.reset(poses); b.reset(poses)
+        b.reserve_noise(T + 2)
+        assert b._noise_rows >= T + 2 and a._noise_rows < 300
+        for t in range(T):
+            a.step(acts[t % 16]); b.step(acts[t % 16])
+            if t % 97 == 0 or t == T - 1:
+                assert torch.equal(a.scans, b.scans) and torch.equal(a.obs_block, b.obs_block), t
+        assert T <= a._noise_rows < T + 130       # grown in chunks of 128 rows, not doubled
+        assert torch.equal(a.noise_step, b.noise_step)
+    torch.cuda.synchronize()
