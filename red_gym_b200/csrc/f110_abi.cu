@@ -162,7 +162,14 @@ extern "C" int f110_create(const f110_config *cfg, int device, f110_sim **out)
     double angle_increment = cfg->fov / (cfg->n_beams - 1);
     d.theta_inc = cfg->theta_dis * angle_increment / (2. * M_PI);
     d.inc_fix = (unsigned long long)(d.theta_inc * 4294967296.0 + 0.5);
-    d.kstep_lo = (unsigned)(32ull * d.inc_fix); d.kstep_hi = (unsigned)((32ull * d.inc_fix) >> 32);
+    {   // a round of 32 beams advances the table index by 32 * inc, taken modulo the table: the kernels wrap a sum of two
+        // indices below theta_dis with ONE conditional subtraction, and with a handful of beams over a wide field of view
+        // (fewer than 32 fov / 2 pi + 1 of them) 32 * inc is more than a turn of the table -- the index fetched ahead for the
+        // next round then lay beyond the table (found by the checked build, tests/test_gpu_edge_cases.py with 2 and 3 beams)
+        const unsigned long long kwrap = (unsigned long long)(unsigned)cfg->theta_dis << 32;
+        const unsigned long long kstep = (32ull * d.inc_fix) % kwrap;
+        d.kstep_lo = (unsigned)kstep; d.kstep_hi = (unsigned)(kstep >> 32);
+    }
     // fp64 beam index (theta_index_of): the reference's running sum drifts from the closed form by at most half an ulp of
     // theta_dis per addition (1.14e-13 at 2000), the closed form itself by an ulp per round of 32 beams; the band within
     // which the running sum is replayed exactly is that bound in units of 2^-30, plus 2 (3 units = 2.8e-9 up to 2160 beams)

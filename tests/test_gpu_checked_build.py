@@ -31,6 +31,8 @@ def test_bounds_checked_build_runs_clean():
 def test_normal_build_has_no_checks():
     import ctypes
     from red_gym_b200 import _native as nat
+    if os.environ.get("F110_B200_LIB"):
+        pytest.skip("another build of the library is selected (tools/checked_run.py runs the suite against the checked one)")
     L = nat.load()
     assert L.f110_build_is_checked() == 0
     out = (ctypes.c_uint64 * 8)()

@@ -24,6 +24,8 @@ DEFAULT = [
     "tests/test_gpu_step.py::test_rollouts_match_reference_goldens",
     "tests/test_gpu_step.py::test_fp32_two_agent_rollout_tracks_fp64_path",
     "tests/test_gpu_abi_v2.py::test_u16_scan_format_is_the_float_scan_rounded_to_half_millimetres",
+    "tests/test_gpu_edge_cases.py::test_raycast_beam_count_edges",
+    "tests/test_gpu_edge_cases.py::test_step_with_other_beam_counts",
 ]
 NAMES = ["edt32_address", "edt64_cell", "table_index", "queue_slot", "order_slot", "beam_index", "noise_row", "selftest"]
 
