@@ -236,8 +236,9 @@ int f110_last_raycast_ms(f110_sim *sim, float *ms);
 int f110_l2_probe(int device, int64_t table_bytes, int32_t repeats, double *out6, void *stream);
 /* Checked build (libf110_b200_checked.so, compiled with -DF110_CHECKED; compute-sanitizer is closed on the B200 pool): every
  * address / index whose bounds test the fast kernels removed or hoisted is tested, violations are counted per device.
- * out8: counts since process start -- 0 padded-fp32-map address, 1 fp64 map cell, 2 trig / direction table index, 3 opponent
- * queue slot, 4 sort bin / slot, 5 beam index, 6 noise row, 7 self-test.  selftest != 0 first commits ONE deliberate violation of
+ * out8: counts since process start -- 0 padded-fp32-map address, 1 fp64 map cell (also the renderer's map cells), 2 trig /
+ * direction table index (also the planner's way-point indices), 3 opponent queue slot (also the rasteriser's line / edge queue),
+ * 4 sort bin / slot, 5 beam index (also the rasteriser's beam picks, pixels and rows), 6 noise row, 7 self-test.  selftest != 0 first commits ONE deliberate violation of
  * kind 7 (counted only by a checked build: proves the checks are compiled in).  f110_build_is_checked(): 1 / 0. */
 int f110_build_is_checked(void);
 int f110_debug_violations(int device, uint64_t *out8, int32_t selftest);

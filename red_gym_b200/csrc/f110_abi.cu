@@ -1028,6 +1028,7 @@ extern "C" int f110_bitmap_create(const f110_bitmap_config *cfg, const int32_t *
     b->device = device;
     F110BitmapDev &d = b->d;
     memset(&d, 0, sizeof(d));
+    d.violations = violations_for(device);
     const int T = cfg->target_beam_count;
     d.n_beams = cfg->n_beams; d.n_points = T; d.height = cfg->height; d.width = cfg->width;
     d.wpr = (cfg->width + 31) / 32;
@@ -1102,6 +1103,7 @@ extern "C" int f110_pursuit_create(const double *wx, const double *wy, const dou
     if (e != cudaSuccess) { cudaFree(p->tables); delete p; return fail(F110_ERR_CUDA, "waypoint upload failed: %s", cudaGetErrorString(e)); }
     p->d.n_waypoints = n; p->d.wheelbase = wheelbase; p->d.max_reacquire = max_reacquire;
     p->d.wx = p->tables; p->d.wy = p->tables + n; p->d.wv = p->tables + 2 * (size_t)n;
+    p->d.violations = violations_for(device);
     *out = p;
     return F110_OK;
 }
@@ -1164,6 +1166,7 @@ extern "C" int f110_render_create(const f110_render_config *cfg, const uint8_t *
     d.map_h = cfg->map_h; d.map_w = cfg->map_w; d.res = cfg->resolution; d.ox = cfg->origin_x; d.oy = cfg->origin_y;
     d.obstacle = r->obstacle; d.follow_margin = cfg->follow_margin;
     d.left = cfg->left; d.right = cfg->right; d.bottom = cfg->bottom; d.top = cfg->top;
+    d.violations = violations_for(device);
     *out = r;
     return F110_OK;
 }

@@ -16,6 +16,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "f110_bitmap_dev.h"
+#include "f110_dev.h"      // F110_CHECK / F110_V_*: the checked build tests every pixel, row and queue slot below
 
 #define XY_SHIFT 16
 #define XY_ONE (1 << XY_SHIFT)
@@ -58,8 +59,12 @@ static __device__ __forceinline__ bool clip_line(int w, int h, long long &x1, lo
     return (c1 | c2) == 0;
 }
 
-static __device__ __forceinline__ void set_px(unsigned *mask, int wpr, int x, int y)
+// what the checked build needs to test a pixel; in the normal build nothing reads it and it is compiled away
+struct BmChk { unsigned long long *v; int w, h; };
+
+static __device__ __forceinline__ void set_px(unsigned *mask, int wpr, int x, int y, const BmChk &chk)
 {
+    F110_CHECK(chk.v, (unsigned)x < (unsigned)chk.w && (unsigned)y < (unsigned)chk.h, F110_V_BEAM);     // clipping is the only bounds test a line has
     atomicOr(mask + y * wpr + (x >> 5), 1u << (x & 31));
 }
 
@@ -86,7 +91,7 @@ static __device__ __forceinline__ bool line_setup(int w, int h, int ax, int ay, 
 // LineIterator: the minor coordinate advances when err < 0; err starts at dx - 2 dy, loses 2 dy per step and gains 2 dx
 // per minor step, so before pixel i the minor offset is m_i = floor((2 dy i + dx - 1) / (2 dx)) and
 // err_i = dx - 2 dy (i + 1) + 2 dx m_i: a span can start anywhere.
-static __device__ __forceinline__ void line_span(unsigned *mask, int wpr, const LineJob &j, int i0, int i1)
+static __device__ __forceinline__ void line_span(unsigned *mask, int wpr, const LineJob &j, int i0, int i1, const BmChk &chk)
 {
     if (i0 >= i1) return;
     int m = 0;
@@ -96,8 +101,8 @@ static __device__ __forceinline__ void line_span(unsigned *mask, int wpr, const 
     }
     int err = j.dx - 2 * j.dy * (i0 + 1) + 2 * j.dx * m;
     for (int i = i0; i < i1; i++) {
-        if (j.vert) set_px(mask, wpr, j.px + m, j.py + j.sy * i);
-        else set_px(mask, wpr, j.px + i, j.py + j.sy * m);
+        if (j.vert) set_px(mask, wpr, j.px + m, j.py + j.sy * i, chk);
+        else set_px(mask, wpr, j.px + i, j.py + j.sy * m, chk);
         const bool neg = err < 0;
         err += -2 * j.dy + (neg ? 2 * j.dx : 0);
         m += neg ? 1 : 0;
@@ -144,10 +149,11 @@ static __device__ __forceinline__ bool edge_setup(int w, int h, int p0x, int p0y
 }
 
 static __device__ __forceinline__ void edge_rows(unsigned *par, unsigned *exact, unsigned *carry, int wpr, int w, const EdgeJob &e,
-                                                 int y0, int y1)
+                                                 int y0, int y1, const BmChk &chk)
 {
     long long x = e.x + (long long)(y0 - e.ya) * e.dx;
     for (int y = y0; y < y1; y++, x += e.dx) {
+        F110_CHECK(chk.v, (unsigned)y < (unsigned)chk.h, F110_V_BEAM);
         const long long a = x >> XY_SHIFT;
         if (a < 0) atomicXor(carry + y, 1u);
         else if (a < w) {
@@ -178,6 +184,7 @@ __global__ void __launch_bounds__(256, 4) k_lidar_bitmap(const F110BitmapDev d, 
     uint2 *lut = (uint2 *)(smem + ((2 * T + 3 * H * wpr + H + 2 * T + 4 + 1) & ~1));   // 256 entries: 8 mask bits -> 8 bytes of bg / fg
     const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, wid = tid >> 5, nw = nt >> 5;
     const bool rays = d.draw_mode == F110_BM_RAYS, fill = d.draw_mode == F110_BM_FILL;
+    const BmChk chk = { d.violations, W, H };
     for (int b = tid; b < 256; b += nt) {
         const unsigned bg = d.bg * 0x01010101u, fx = (d.fg ^ d.bg) * 0x01010101u;
         const unsigned m0 = (((b & 15u) * 0x00204081u) & 0x01010101u) * 0xffu, m1 = ((((b >> 4) & 15u) * 0x00204081u) & 0x01010101u) * 0xffu;
@@ -186,6 +193,7 @@ __global__ void __launch_bounds__(256, 4) k_lidar_bitmap(const F110BitmapDev d, 
     for (long long img = blockIdx.x; img < n; img += gridDim.x) {
         // polar -> pixel (lidar.py:71-83): rint(c + (scaling_factor * data) * cos(angle))
         for (int t = tid; t < T; t += nt) {
+            F110_CHECK(d.violations, d.indices[t] >= 0 && d.indices[t] < d.n_beams, F110_V_BEAM);
             const size_t src = (size_t)img * d.n_beams + d.indices[t];
             double sd;
             if (d.scan_is_f32) sd = (double)(d.scale32 * ((const float *)scans)[src]);
@@ -202,15 +210,23 @@ __global__ void __launch_bounds__(256, 4) k_lidar_bitmap(const F110BitmapDev d, 
             const int2 p0 = rays ? make_int2(d.cx, d.cy) : pts[t ? t - 1 : T - 1];
             LineJob lj;
             if (line_setup(W, H, p0.x, p0.y, p1.x, p1.y, lj)) {
-                if (lj.dx < BM_SHORT) line_span(mask, wpr, lj, 0, lj.dx + 1);
-                else queue[atomicAdd(qn, 1u)] = (unsigned)t;
+                if (lj.dx < BM_SHORT) line_span(mask, wpr, lj, 0, lj.dx + 1, chk);
+                else {
+                    const unsigned slot = atomicAdd(qn, 1u);
+                    F110_CHECK(d.violations, slot < 2u * (unsigned)T, F110_V_QUEUE);
+                    queue[slot] = (unsigned)t;
+                }
             }
             if (rays) fill_box(mask, wpr, W, H, p1.x, p1.y, true);
             if (fill) {
                 EdgeJob ej;
                 if (edge_setup(W, H, p0.x, p0.y, p1.x, p1.y, ej)) {
-                    if (ej.yb - ej.ya <= BM_SHORT) edge_rows(par, exact, carry, wpr, W, ej, ej.ya, ej.yb);
-                    else queue[atomicAdd(qn, 1u)] = (unsigned)t | 0x80000000u;
+                    if (ej.yb - ej.ya <= BM_SHORT) edge_rows(par, exact, carry, wpr, W, ej, ej.ya, ej.yb, chk);
+                    else {
+                        const unsigned slot = atomicAdd(qn, 1u);
+                        F110_CHECK(d.violations, slot < 2u * (unsigned)T, F110_V_QUEUE);
+                        queue[slot] = (unsigned)t | 0x80000000u;
+                    }
                 }
             }
         }
@@ -220,6 +236,7 @@ __global__ void __launch_bounds__(256, 4) k_lidar_bitmap(const F110BitmapDev d, 
         for (int k = wid; k < nq; k += nw) {
             const unsigned e = queue[k];
             const int t = (int)(e & 0x7fffffffu);
+            F110_CHECK(d.violations, t < T, F110_V_QUEUE);
             const int2 p1 = pts[t];
             const int2 p0 = rays ? make_int2(d.cx, d.cy) : pts[t ? t - 1 : T - 1];
             if (e & 0x80000000u) {
@@ -227,12 +244,12 @@ __global__ void __launch_bounds__(256, 4) k_lidar_bitmap(const F110BitmapDev d, 
                 edge_setup(W, H, p0.x, p0.y, p1.x, p1.y, ej);
                 const int rows = ej.yb - ej.ya, per = (rows + 31) >> 5;
                 const int y0 = ej.ya + lane * per;
-                edge_rows(par, exact, carry, wpr, W, ej, min(y0, ej.yb), min(y0 + per, ej.yb));
+                edge_rows(par, exact, carry, wpr, W, ej, min(y0, ej.yb), min(y0 + per, ej.yb), chk);
             } else {
                 LineJob lj;
                 line_setup(W, H, p0.x, p0.y, p1.x, p1.y, lj);
                 const int per = (lj.dx + 1 + 31) >> 5;
-                line_span(mask, wpr, lj, min(lane * per, lj.dx + 1), min(lane * per + per, lj.dx + 1));
+                line_span(mask, wpr, lj, min(lane * per, lj.dx + 1), min(lane * per + per, lj.dx + 1), chk);
             }
         }
         __syncthreads();

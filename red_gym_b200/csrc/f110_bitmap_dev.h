@@ -18,6 +18,7 @@ struct F110BitmapDev {
     float scale32;        // float32(scaling_factor): numpy multiplies a float32 scan by it in float32
     const int *indices;   // [n_points] np.linspace(0, B - 1, T, dtype=int)
     const double *cosa, *sina;   // [n_points] np.cos / np.sin of the beam angles
+    unsigned long long *violations;   // the device's F110_V_* counters (checked build only: f110_dev.h)
 };
 
 void f110_launch_bitmap(const F110BitmapDev &d, const void *scans, long long n, uint8_t *out, int packed, cudaStream_t st);

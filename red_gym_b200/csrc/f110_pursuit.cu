@@ -18,6 +18,7 @@
 #include <math_constants.h>
 #include <stdint.h>
 #include "f110_pursuit_dev.h"
+#include "f110_dev.h"      // F110_CHECK / F110_V_*
 
 static __device__ __forceinline__ bool circle_hit(const double *wx, const double *wy, int i0, int i1, double px, double py,
                                                   double radius, double &t1, double &t2)
@@ -120,6 +121,7 @@ __global__ void __launch_bounds__(128) k_pure_pursuit(const F110PursuitDev d, co
         const int start_i = (int)tt;
         const double start_t = tt - floor(tt);            // t % 1.0, t >= 0
         double t1, t2;
+        F110_CHECK(d.violations, start_i >= 0 && start_i < nw, F110_V_TABLE);
         for (int i = start_i; i < nw - 1 && !have; i++) {
             if (!circle_hit(wx, wy, i, i + 1, px, py, ld, t1, t2)) continue;
             if (i == start_i) {
@@ -128,14 +130,20 @@ __global__ void __launch_bounds__(128) k_pure_pursuit(const F110PursuitDev d, co
         }
         for (int i = -1; i < start_i && !have; i++) {     // wrap around to the beginning of the trajectory
             const int i0 = i < 0 ? i + nw : i % nw, i1 = (i + 1) % nw;
+            F110_CHECK(d.violations, i0 >= 0 && i0 < nw && i1 >= 0 && i1 < nw, F110_V_TABLE);
             if (!circle_hit(wx, wy, i0, i1, px, py, ld, t1, t2)) continue;
             if ((t1 >= 0.0 && t1 <= 1.0) || (t2 >= 0.0 && t2 <= 1.0)) { have = true; i2 = i; }
         }
-        if (have) { const int k = i2 < 0 ? i2 + nw : i2; tx = wx[k]; ty = wy[k]; }     // wpts[i2] (python index -1 = last)
+        if (have) {      // wpts[i2] (python index -1 = last)
+            const int k = i2 < 0 ? i2 + nw : i2;
+            F110_CHECK(d.violations, k >= 0 && k < nw, F110_V_TABLE);
+            tx = wx[k]; ty = wy[k];
+        }
     } else if (bd < d.max_reacquire) {
         have = true; i2 = bi; tx = wx[bi]; ty = wy[bi];
     }
     double speed = 4.0, steer = 0.0;
+    F110_CHECK(d.violations, bi >= 0 && bi < nw, F110_V_TABLE);
     if (have) {
         // get_actuation
         const double wyl = sin(-th) * (tx - px) + cos(-th) * (ty - py);

@@ -6,6 +6,7 @@ struct F110PursuitDev {
     int n_waypoints;
     double wheelbase, max_reacquire;
     const double *wx, *wy, *wv;      // [n_waypoints] x, y, speed columns of the raceline file
+    unsigned long long *violations;  // the device's F110_V_* counters (checked build only: f110_dev.h)
 };
 
 void f110_launch_pursuit(const F110PursuitDev &d, const double *x, const double *y, const double *theta, long long n,

@@ -9,6 +9,7 @@
 // Compiled with -fmad=false (same rounding as the numpy restatement the tests compare against).
 #include <math.h>
 #include "f110_render_dev.h"
+#include "f110_dev.h"      // F110_CHECK / F110_V_*
 
 #define CAR_LENGTH 0.58
 #define CAR_WIDTH 0.31
@@ -72,6 +73,7 @@ __global__ void __launch_bounds__(256) k_render(const F110RenderDev d, const dou
     cell_range(left, right, d.width, px, d.res, d.ox, d.map_w, c0, c1);
     cell_range(bottom, top, d.height, py, d.res, d.oy, d.map_h, r0, r1);
     bool hit = false;
+    F110_CHECK(d.violations, r0 >= 0 && r1 <= d.map_h && c0 >= 0 && c1 <= d.map_w, F110_V_EDT64);      // cell_range clamps to the map
     for (int rr = r0; rr < r1 && !hit; rr++)
         for (int cc = c0; cc < c1; cc++)
             if (d.obstacle[(size_t)rr * d.map_w + cc]) { hit = true; break; }

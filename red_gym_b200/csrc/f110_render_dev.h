@@ -11,6 +11,7 @@ struct F110RenderDev {
     const uint8_t *obstacle;    // [map_h][map_w] 1 where the flipped map image is exactly 0 (rendering.py:150)
     double follow_margin;       // >= 0: camera = ego car's bounding box +- margin (examples/waypoint_follow.py:259-269)
     double left, right, bottom, top;   // fixed camera otherwise (glOrtho, rendering.py:290)
+    unsigned long long *violations;    // the device's F110_V_* counters (checked build only: f110_dev.h)
 };
 
 void f110_launch_render(const F110RenderDev &d, const double *x, const double *y, const double *theta, long long n_envs,
