@@ -875,10 +875,18 @@ __global__ void __launch_bounds__(AG_THREADS, 8) k_agents(const F110Dev d)
             const float R = 0.5f * sqrtf((float)(len * len + wid * wid)) * 1.0001f;
             double off = yaw - (double)atan2f((float)cy, (float)cx);
             off -= 2 * PI_() * rint(off / (2 * PI_()));
-            double par = yaw - d.pose_pre[2 * (size_t)NA + base + o];
+            const double yaw_o = d.pose_pre[2 * (size_t)NA + base + o];
+            double par = yaw - yaw_o;
             par -= PI_() / 2 * rint(par / (PI_() / 2));
             float cone = (dist > 1.001f * R) ? asinf(R / dist) + 2e-3f : 4.0f;   // inside the circle (or NaN): every beam
             if (!(cone == cone) || !(off == off)) { cone = 4.0f; off = 0.0; }
+            // Both tests take a beam's direction to be yaw + scan_angle.  The reference rounds that sum (pose[2] + scan_angles[i],
+            // laser_models.py:343), and the yaw is only wrapped by 2 pi once per step (base_classes.py:398-402): a car whose model
+            // has blown up (yaw rate 1e17 with a harsh parameter set and dt = 0.02 in tools/step_fuzz.py) has a yaw of 1e15, where
+            // doubles are 0.125 rad apart, six neighbouring beams point the same way and hit what the exact directions miss.
+            // Far outside any yaw a wrapped heading can have, no beam is skipped: the reference's full window is cast.
+            if (!(fabs(yaw) < 1e6)) { cone = 4.0f; off = 0.0; }
+            if (!(fabs(yaw) < 1e6) || !(fabs(yaw_o) < 1e6)) par = CUDART_NAN;
             span[2][t] = __float_as_int((float)off);
             span[3][t] = __float_as_int(cone);
             span[4][t] = __float_as_int((float)par);      // NaN: every beam counts as parallel

@@ -141,3 +141,36 @@ def test_sort_thresholds_per_precision(dtype, N):
     assert (a.launch_count - l0[0]) - (b.launch_count - l0[1]) == 3 * T          # the three sort kernels, every step
     assert below.launch_count - l0[2] == 3 * T                                   # one scan below the threshold: no sort
     assert torch.equal(below.obs_block, a.obs_block[:, :N - 1])                  # ... and the same results
+
+
+def test_opponent_cast_with_a_yaw_far_outside_one_turn():
+    """The reference wraps the yaw by 2 pi once per step only (base_classes.py:398-402) and casts opponents along
+    pose[2] + scan_angles[i] as rounded (laser_models.py:343): at a yaw of 1e15 doubles are 0.125 rad apart and neighbouring
+    beams share a direction.  The library's beam filter (cone around the opponent, edge-parallel beams) assumes exact
+    directions and must step aside there (found by tools/step_fuzz.py: a car whose model blew up under a harsh parameter set)."""
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    N, A = 240, 3
+    rng = np.random.default_rng(5)
+    poses = np.repeat(raceline_poses(N)[:, None, :], A, axis=1)
+    poses[:, 1:, 0] += rng.uniform(-2.0, 2.0, (N, A - 1))
+    poses[:, 1:, 1] += rng.uniform(-2.0, 2.0, (N, A - 1))
+    big = np.array([5.9028286868952100e+14, -3.3e12, 1.0e7, 7.7e9, 2.5e15, -8.1e13])
+    poses[:, :, 2] = rng.uniform(-3, 3, (N, A))
+    poses[:, 0, 2] = big[np.arange(N) % big.size] + rng.uniform(-3, 3, N)          # the scanning car's yaw
+    poses[N // 2:, 1, 2] = big[np.arange(N - N // 2) % big.size]                     # an opponent's yaw
+    kw = dict(map=os.path.join(MAPS, "example_map"), seed=9, num_beams=540, fov=4.7)
+    for dtype in ("fp64", "fp32"):
+        env = BatchF110Env(num_envs=N, num_agents=A, dtype=dtype, noise="off" if dtype == "fp32" else "numpy", **kw)
+        ora = fo.OracleEnv(N, A, noise_rows=8, noise=(dtype == "fp64"), **kw)
+        env.reset(poses); ora.reset(poses)
+        changed = 0
+        for t in range(3):
+            act = np.stack([rng.uniform(-0.3, 0.3, (N, A)), rng.uniform(0.0, 3.0, (N, A))], axis=-1)
+            env.step(act); ora.step(act)
+            off = np.abs(env.scans.cpu().numpy() - ora.scans) > (SCAN_TOL if dtype == "fp64" else 2e-2)
+            # fp64: a beam may graze a corner differently in the last ulp of sin / cos of a huge argument; whole groups of beams may not
+            assert off.sum(axis=2).max() <= (2 if dtype == "fp64" else 12), (dtype, t, np.argwhere(off.sum(axis=2) > 2)[:5])
+            assert (env.collision_idx.cpu().numpy() == ora.collision_idx).all()
+            changed += int((ora.scans < 29.0).sum())
+        assert changed > 0
