@@ -673,7 +673,9 @@ static int check_ready(f110_sim *s)
 static bool use_fused(const f110_sim *s)
 {
     const F110Dev &d = s->d;
-    return !d.scan_is_f32 && d.n_agents == 1 && d.n_envs <= F110_FUSED_MAX_ENVS && !(s->cfg.raycast_variant & (128 | 256));   // variant bits 7 / 8: three-kernel step
+    if (d.scan_is_f32 || (s->cfg.raycast_variant & (128 | 256))) return false;       // variant bits 7 / 8: the step kernel by kernel
+    if (d.n_agents == 1) return d.n_envs <= F110_FUSED_MAX_ENVS;
+    return d.n_agents <= F110_FUSED_MULTI_MAX_AGENTS && d.n_envs <= F110_FUSED_MULTI_MAX_ENVS && d.n_envs <= d.n_sm && !d.count_lookups;
 }
 
 // kernels of one step, in the order of Simulator.step + F110Env.step.  host_*: mapped host buffers the fused

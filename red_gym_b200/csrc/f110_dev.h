@@ -126,6 +126,9 @@ void f110_launch_step_fused64(const F110Dev &d, double *obs_host, double *scans_
                               cudaStream_t st);
 // launches of at most this many single-agent fp64 envs take the fused kernel (a CTA per env, about one wave at 128 registers)
 #define F110_FUSED_MAX_ENVS 296
+// ... and for envs of 2 .. 8 agents: a CTA of 32 warps per env, one wave (k_step_fused_multi64)
+#define F110_FUSED_MULTI_MAX_AGENTS 8
+#define F110_FUSED_MULTI_MAX_ENVS 148
 // order: null or a permutation of [0, n): warp w scans pose order[w]
 void f110_launch_scan_only64(const F110Dev &d, const double *poses, int n, double *out, const int *order, int variant, cudaStream_t st);
 void f110_launch_scan_only32(const F110Dev &d, const double *poses, int n, float *out, const int *order, int variant, cudaStream_t st);

@@ -10,6 +10,7 @@
 //   k_reset      thread per (env, agent)                                     (base_classes.py:181-202, f110_env.py:318-329)
 #include <cuda_runtime.h>
 #include <math_constants.h>
+#include <string.h>
 #include "f110_dev.h"
 
 #define FULL 0xffffffffu
@@ -784,15 +785,18 @@ static __device__ __forceinline__ int nearest_beam(const F110Dev &d, double targ
 // pass; the four fp64 edge intersections then run on full batches of 32 pairs.  Results are identical to casting
 // every beam; 131072 agents: 1.50 ms (warp per agent, all beams) -> DESIGN.md.
 #define AG_THREADS 128
-// one (record, beam) pair: item = record slot in the warp << 16 | beam
-template <typename SCAN_T>
-static __device__ __forceinline__ void agents_cast(const F110Dev &d, const double (*rec)[AG_THREADS], int w0, int ia0, int item)
+// one (record, beam) pair: item = record slot in the warp << 16 | beam.  span[5] holds the scanning agent of a record.
+// ATOMIC: records of the same agent are cast by different warps at the same time (k_step_fused_multi64) -- the minimum is
+// taken on the bit pattern as a signed integer, which orders doubles like the comparison does whenever the new range is
+// not negative (a range never is; a scan value with noise may be, and then stays, as in the reference)
+template <typename SCAN_T, bool ATOMIC>
+static __device__ __forceinline__ void agents_cast(const F110Dev &d, const double (*rec)[AG_THREADS], const int (*span)[AG_THREADS], int w0, int item)
 {
     const int s = w0 + (item >> 16), i = item & 0xffff;
     const double qx = rec[0][s], qy = rec[1][s];
     double v3s, v3c;
     sincos((rec[2][s] + __ldg(d.scan_angles + i)) + PI_() / 2., &v3s, &v3c);
-    SCAN_T *scan = (SCAN_T *)d.scans + (size_t)(ia0 + s) * d.n_beams + i;
+    SCAN_T *scan = (SCAN_T *)d.scans + (size_t)span[5][s] * d.n_beams + i;
     double r = (double)*scan;
     const double r0 = r;
     double ax = rec[9][s], ay = rec[10][s];        // corner 3, then edges 3-0, 0-1, 1-2, 2-3: min() does not care about the order
@@ -803,22 +807,151 @@ static __device__ __forceinline__ void agents_cast(const F110Dev &d, const doubl
         if (rr < r) r = rr;
         ax = bx; ay = by;
     }
-    if (r < r0) *scan = (SCAN_T)r;
+    if (r < r0) {
+        if (ATOMIC) atomicMin((long long *)scan, __double_as_longlong(r));
+        else *scan = (SCAN_T)r;
+    }
 }
 
-template <typename SCAN_T>
-// 8 CTAs of 128 threads per SM (64 registers, 240 bytes of spill): measured on config 4 (131 072 agents) against the compiler's own
-// choice (96 registers, 5 CTAs) and 6 / 10 / 12 CTAs: step 1.887 ms against 1.937 / 1.951 / 1.937 / 1.991 (profiles/r2g_agents_occupancy_ab.json)
-__global__ void __launch_bounds__(AG_THREADS, 8) k_agents(const F110Dev d)
+// Simulator.check_collision for agent a of env e (base_classes.py:529-543) on the pre-iTTC poses with the construct-time car
+// size: pair (min, max) of every partner; collision_idx = last writer = largest partner that collides
+static __device__ __forceinline__ void agent_collision(const F110Dev &d, int ia, int e, int a)
 {
-    __shared__ double rec[11][AG_THREADS];      // px, py, yaw, corner x/y * 4 of the current opponent
-    __shared__ int span[5][AG_THREADS];         // first / last blocked beam (empty: 1, 0); float bits: bearing offset, cone, edge offset
-    __shared__ int queue[AG_THREADS / 32][64];  // per warp: (record, beam) pairs waiting for a full batch
     const int NA = d.n_envs * d.n_agents, A = d.n_agents;
-    const int t = threadIdx.x, lane = t & 31, w0 = t & ~31, wq = t >> 5;
-    const int ia = blockIdx.x * AG_THREADS + t;
+    const size_t base = (size_t)e * A;
+    const double gw = d.params[F110_NP * A + 0], gl = d.params[F110_NP * A + 1];
+    double va[4][2], vo[4][2];
+    get_vertices(d.pose_pre[ia], d.pose_pre[(size_t)NA + ia], d.pose_pre[2 * (size_t)NA + ia], gl, gw, va);
+    int last = -1;
+    for (int o = 0; o < A; o++) {
+        if (o == a) continue;
+        get_vertices(d.pose_pre[base + o], d.pose_pre[NA + base + o], d.pose_pre[2 * (size_t)NA + base + o], gl, gw, vo);
+        if (a < o ? gjk_collision(va, vo) : gjk_collision(vo, va)) last = o;
+    }
+    d.collision_idx[ia] = (double)last;
+    d.collisions[ia] = (last >= 0 || d.in_collision[ia]) ? 1.0 : 0.0;
+}
+
+// RaceCar.ray_cast_agents, the part per (agent, opponent): the record of opponent o (agent base + o) as seen by agent ia at
+// (px, py, yaw) -- own pose AFTER the iTTC zeroing, the opponent's from before it, drawn with THIS agent's length / width --
+// into column t: rec = px, py, yaw, corner x / y * 4; span = first / last blocked beam (get_blocked_view_indices,
+// laser_models.py:283-315), float bits of bearing offset, cone, edge offset; scanning agent
+static __device__ __forceinline__ void agent_pair_record(const F110Dev &d, double (*rec)[AG_THREADS], int (*span)[AG_THREADS], int t, int ia,
+                                                         size_t base, int o, double px, double py, double yaw, double ego_ang, double len, double wid)
+{
+    const int NA = d.n_envs * d.n_agents;
+    double v[4][2];
+    get_vertices(d.pose_pre[base + o], d.pose_pre[NA + base + o], d.pose_pre[2 * (size_t)NA + base + o], len, wid, v);
+    int mn = 0x7fffffff, mx = -1;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        double vx = v[k][0] - px, vy = v[k][1] - py;
+        double nrm = sqrt(vx * vx + vy * vy);
+        double angle = ego_ang - atan2(vy / nrm, vx / nrm);
+        if (angle > PI_()) angle = angle - 2 * PI_();
+        else if (angle < -PI_()) angle = angle + 2 * PI_();
+        int b = nearest_beam(d, -angle);
+        mn = min(mn, b); mx = max(mx, b);
+        rec[3 + 2 * k][t] = v[k][0];
+        rec[4 + 2 * k][t] = v[k][1];
+    }
+    rec[0][t] = px; rec[1][t] = py; rec[2][t] = yaw;
+    // (a): bearing of the centre relative to scan angle 0 and the half angle of the bounding circle; (b): edge directions
+    const double cx = 0.25 * (((v[0][0] + v[1][0]) + v[2][0]) + v[3][0]) - px;
+    const double cy = 0.25 * (((v[0][1] + v[1][1]) + v[2][1]) + v[3][1]) - py;
+    const float dist = sqrtf((float)(cx * cx + cy * cy));
+    const float R = 0.5f * sqrtf((float)(len * len + wid * wid)) * 1.0001f;
+    double off = yaw - (double)atan2f((float)cy, (float)cx);
+    off -= 2 * PI_() * rint(off / (2 * PI_()));
+    const double yaw_o = d.pose_pre[2 * (size_t)NA + base + o];
+    double par = yaw - yaw_o;
+    par -= PI_() / 2 * rint(par / (PI_() / 2));
+    float cone = (dist > 1.001f * R) ? asinf(R / dist) + 2e-3f : 4.0f;   // inside the circle (or NaN): every beam
+    if (!(cone == cone) || !(off == off)) { cone = 4.0f; off = 0.0; }
+    // Both tests take a beam's direction to be yaw + scan_angle.  The reference rounds that sum (pose[2] + scan_angles[i],
+    // laser_models.py:343), and the yaw is only wrapped by 2 pi once per step (base_classes.py:398-402): a car whose model
+    // has blown up (yaw rate 1e17 with a harsh parameter set and dt = 0.02 in tools/step_fuzz.py) has a yaw of 1e15, where
+    // doubles are 0.125 rad apart, six neighbouring beams point the same way and hit what the exact directions miss.
+    // Far outside any yaw a wrapped heading can have, no beam is skipped: the reference's full window is cast.
+    if (!(fabs(yaw) < 1e6)) { cone = 4.0f; off = 0.0; }
+    if (!(fabs(yaw) < 1e6) || !(fabs(yaw_o) < 1e6)) par = CUDART_NAN;
+    span[0][t] = mn; span[1][t] = mx;
+    span[2][t] = __float_as_int((float)off);
+    span[3][t] = __float_as_int(cone);
+    span[4][t] = __float_as_int((float)par);      // NaN: every beam counts as parallel
+    span[5][t] = ia;
+}
+
+// ray_cast (laser_models.py:318-346) over the candidate beams of record s (item code `code`: s = w0 + code): the calling warp
+// queues them in queue_w (`fill` entries so far) and casts every full batch of 32.  The reference casts every beam between the
+// first and last blocked index; only beams that pass test (a) or (b) above can change.  n_units > 1: the walk is shared by
+// n_units warps, each taking the 32-beam steps whose running number `unit` is its own (my_unit) modulo n_units.
+template <typename SCAN_T, bool ATOMIC>
+static __device__ __forceinline__ void agents_walk_record(const F110Dev &d, const double (*rec)[AG_THREADS], const int (*span)[AG_THREADS],
+                                                          int *queue_w, int &fill, int s, int code, int w0, int lane, float a032, float inc32,
+                                                          float inv_inc32, int &unit, int n_units, int my_unit)
+{
+    const int first = span[0][s], lastb = span[1][s];
+    if (first > lastb) return;
+    const float off = __int_as_float(span[2][s]), cone = __int_as_float(span[3][s]), par = __int_as_float(span[4][s]);
+    // windows 2 (cone + 2 beams) wide, pi apart: disjoint under these limits; otherwise one pass over [first, last]
+    const bool windows = cone < 1.2f && inc32 < 0.05f && inc32 > 0.0015f && d.fov <= 6.2831854;
+    const float half = cone * inv_inc32 + 2.0f;
+    // passes: -1, 0, 1 = beams within `cone` of the bearing (- 2 pi, + 0, + 2 pi); 2 = the (at most five) beam
+    // directions parallel to an edge, one lane per candidate and neighbour (2e-3 rad < 1.5 beams)
+    for (int n = windows ? -1 : 0; n <= (windows ? 2 : 0); n++) {
+        int lo = first, hi = lastb;
+        if (windows && n < 2) {
+            const float c = ((float)n * 6.28318531f - off - a032) * inv_inc32;
+            lo = max(first, (int)ceilf(c - half));
+            hi = min(lastb, (int)floorf(c + half));
+        }
+        if (n == 2) { lo = 0; hi = 14; }
+        for (int i0 = lo; i0 <= hi; i0 += 32) {
+            if (n_units > 1 && (unit++ % n_units) != my_unit) continue;
+            int i = i0 + lane;
+            bool inside = i <= hi;
+            if (n == 2) {
+                const int m = lane / 3;
+                i = __float2int_rn(((float)(m - 2) * 1.57079633f - par - a032) * inv_inc32) + (lane - 3 * m - 1);
+                inside = lane < 15 && i >= first && i <= lastb;
+            }
+            float rel = fmaf((float)i, inc32, a032) + off;
+            rel -= 6.28318531f * rintf(rel * 0.159154943f);
+            float rp = fmaf((float)i, inc32, a032) + par;
+            rp -= 1.57079633f * rintf(rp * 0.636619772f);
+            const bool towards = !(fabsf(rel) > cone);
+            const bool away = !(3.14159265f - fabsf(rel) > cone) && !(fabsf(rp) > 2e-3f);
+            const bool take = inside && (n == 2 ? (away && !towards) : (windows ? towards : (towards || away)));
+            const unsigned m = __ballot_sync(FULL, take);
+            F110_CHECK(d.violations, !take || (fill + __popc(m & ((1u << lane) - 1u)) < 64 && i >= 0 && i < d.n_beams), F110_V_QUEUE);
+            if (take) queue_w[fill + __popc(m & ((1u << lane) - 1u))] = (code << 16) | i;
+            fill += __popc(m);
+            __syncwarp();
+            if (fill >= 32) {
+                agents_cast<SCAN_T, ATOMIC>(d, rec, span, w0, queue_w[lane]);
+                __syncwarp();
+                const int rest = queue_w[32 + lane];
+                __syncwarp();
+                queue_w[lane] = rest;
+                fill -= 32;
+                __syncwarp();
+            }
+        }
+    }
+}
+
+// Simulator.check_collision + RaceCar.ray_cast_agents for all agents (base_classes.py:204-225, 529-543), thread t of a CTA
+// of AG_THREADS threads = agent ia: the scalar fp64 work per agent and per opponent (vertices, GJK, four atan2) by its
+// thread, 32 agents per warp, which leaves a record per opponent in shared memory; the warp then walks its 32 records.
+template <typename SCAN_T>
+static __device__ __forceinline__ void agents_body(const F110Dev &d, double (*rec)[AG_THREADS], int (*span)[AG_THREADS], int (*queue)[64],
+                                                   const int t, const int ia, const bool in_range)
+{
+    const int NA = d.n_envs * d.n_agents, A = d.n_agents;
+    const int lane = t & 31, w0 = t & ~31, wq = t >> 5;
     int e = 0, a = 0;
-    bool live = ia < NA;
+    bool live = in_range;
     if (live) {
         e = ia / A; a = ia - e * A;
         if (d.step_mask && !d.step_mask[e]) live = false;
@@ -826,21 +959,7 @@ __global__ void __launch_bounds__(AG_THREADS, 8) k_agents(const F110Dev d)
     const size_t base = (size_t)e * A;
     double px = 0, py = 0, yaw = 0, ego_ang = 0, len = 0, wid = 0;
     if (live) {
-        // Simulator.check_collision on the pre-iTTC poses with the construct-time car size: pair (min, max) of
-        // every partner; collision_idx = last writer = largest partner that collides
-        const double gw = d.params[F110_NP * A + 0], gl = d.params[F110_NP * A + 1];
-        double va[4][2], vo[4][2];
-        get_vertices(d.pose_pre[ia], d.pose_pre[(size_t)NA + ia], d.pose_pre[2 * (size_t)NA + ia], gl, gw, va);
-        int last = -1;
-        for (int o = 0; o < A; o++) {
-            if (o == a) continue;
-            get_vertices(d.pose_pre[base + o], d.pose_pre[NA + base + o], d.pose_pre[2 * (size_t)NA + base + o], gl, gw, vo);
-            if (a < o ? gjk_collision(va, vo) : gjk_collision(vo, va)) last = o;
-        }
-        d.collision_idx[ia] = (double)last;
-        d.collisions[ia] = (last >= 0 || d.in_collision[ia]) ? 1.0 : 0.0;
-        // RaceCar.ray_cast_agents: own pose AFTER iTTC zeroing, opponents' poses from before it, opponents drawn
-        // with THIS agent's length/width
+        agent_collision(d, ia, e, a);
         px = d.state[ia]; py = d.state[(size_t)NA + ia]; yaw = d.state[4 * (size_t)NA + ia];
         len = d.params[F110_NP * a + F110_P_LENGTH]; wid = d.params[F110_NP * a + F110_P_WIDTH];
         double esn, ecs;
@@ -849,105 +968,27 @@ __global__ void __launch_bounds__(AG_THREADS, 8) k_agents(const F110Dev d)
     }
     const float a032 = (float)__ldg(d.scan_angles), inc32 = (float)(d.fov / (double)(d.n_beams - 1)), inv_inc32 = 1.0f / inc32;
     for (int o = 0; o < A; o++) {
-        int mn = 1, mx = 0;
-        if (live && o != a) {
-            double v[4][2];
-            get_vertices(d.pose_pre[base + o], d.pose_pre[NA + base + o], d.pose_pre[2 * (size_t)NA + base + o], len, wid, v);
-            // get_blocked_view_indices (laser_models.py:283-315)
-            mn = 0x7fffffff; mx = -1;
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                double vx = v[k][0] - px, vy = v[k][1] - py;
-                double nrm = sqrt(vx * vx + vy * vy);
-                double angle = ego_ang - atan2(vy / nrm, vx / nrm);
-                if (angle > PI_()) angle = angle - 2 * PI_();
-                else if (angle < -PI_()) angle = angle + 2 * PI_();
-                int b = nearest_beam(d, -angle);
-                mn = min(mn, b); mx = max(mx, b);
-                rec[3 + 2 * k][t] = v[k][0];
-                rec[4 + 2 * k][t] = v[k][1];
-            }
-            rec[0][t] = px; rec[1][t] = py; rec[2][t] = yaw;
-            // (a): bearing of the centre relative to scan angle 0 and the half angle of the bounding circle; (b): edge directions
-            const double cx = 0.25 * (((v[0][0] + v[1][0]) + v[2][0]) + v[3][0]) - px;
-            const double cy = 0.25 * (((v[0][1] + v[1][1]) + v[2][1]) + v[3][1]) - py;
-            const float dist = sqrtf((float)(cx * cx + cy * cy));
-            const float R = 0.5f * sqrtf((float)(len * len + wid * wid)) * 1.0001f;
-            double off = yaw - (double)atan2f((float)cy, (float)cx);
-            off -= 2 * PI_() * rint(off / (2 * PI_()));
-            const double yaw_o = d.pose_pre[2 * (size_t)NA + base + o];
-            double par = yaw - yaw_o;
-            par -= PI_() / 2 * rint(par / (PI_() / 2));
-            float cone = (dist > 1.001f * R) ? asinf(R / dist) + 2e-3f : 4.0f;   // inside the circle (or NaN): every beam
-            if (!(cone == cone) || !(off == off)) { cone = 4.0f; off = 0.0; }
-            // Both tests take a beam's direction to be yaw + scan_angle.  The reference rounds that sum (pose[2] + scan_angles[i],
-            // laser_models.py:343), and the yaw is only wrapped by 2 pi once per step (base_classes.py:398-402): a car whose model
-            // has blown up (yaw rate 1e17 with a harsh parameter set and dt = 0.02 in tools/step_fuzz.py) has a yaw of 1e15, where
-            // doubles are 0.125 rad apart, six neighbouring beams point the same way and hit what the exact directions miss.
-            // Far outside any yaw a wrapped heading can have, no beam is skipped: the reference's full window is cast.
-            if (!(fabs(yaw) < 1e6)) { cone = 4.0f; off = 0.0; }
-            if (!(fabs(yaw) < 1e6) || !(fabs(yaw_o) < 1e6)) par = CUDART_NAN;
-            span[2][t] = __float_as_int((float)off);
-            span[3][t] = __float_as_int(cone);
-            span[4][t] = __float_as_int((float)par);      // NaN: every beam counts as parallel
-        }
-        span[0][t] = mn; span[1][t] = mx;
+        if (live && o != a) agent_pair_record(d, rec, span, t, ia, base, o, px, py, yaw, ego_ang, len, wid);
+        else { span[0][t] = 1; span[1][t] = 0; }
         __syncwarp();
-        // ray_cast (laser_models.py:318-346) over the candidate beams of the warp's 32 records
-        int fill = 0;
-        for (int k = 0; k < 32; k++) {
-            const int s = w0 + k;
-            const int first = span[0][s], lastb = span[1][s];
-            if (first > lastb) continue;
-            const float off = __int_as_float(span[2][s]), cone = __int_as_float(span[3][s]), par = __int_as_float(span[4][s]);
-            // windows 2 (cone + 2 beams) wide, pi apart: disjoint under these limits; otherwise one pass over [first, last]
-            const bool windows = cone < 1.2f && inc32 < 0.05f && inc32 > 0.0015f && d.fov <= 6.2831854;
-            const float half = cone * inv_inc32 + 2.0f;
-            // passes: -1, 0, 1 = beams within `cone` of the bearing (- 2 pi, + 0, + 2 pi); 2 = the (at most five) beam
-            // directions parallel to an edge, one lane per candidate and neighbour (2e-3 rad < 1.5 beams)
-            for (int n = windows ? -1 : 0; n <= (windows ? 2 : 0); n++) {
-                int lo = first, hi = lastb;
-                if (windows && n < 2) {
-                    const float c = ((float)n * 6.28318531f - off - a032) * inv_inc32;
-                    lo = max(first, (int)ceilf(c - half));
-                    hi = min(lastb, (int)floorf(c + half));
-                }
-                if (n == 2) { lo = 0; hi = 14; }
-                for (int i0 = lo; i0 <= hi; i0 += 32) {
-                    int i = i0 + lane;
-                    bool inside = i <= hi;
-                    if (n == 2) {
-                        const int m = lane / 3;
-                        i = __float2int_rn(((float)(m - 2) * 1.57079633f - par - a032) * inv_inc32) + (lane - 3 * m - 1);
-                        inside = lane < 15 && i >= first && i <= lastb;
-                    }
-                    float rel = fmaf((float)i, inc32, a032) + off;
-                    rel -= 6.28318531f * rintf(rel * 0.159154943f);
-                    float rp = fmaf((float)i, inc32, a032) + par;
-                    rp -= 1.57079633f * rintf(rp * 0.636619772f);
-                    const bool towards = !(fabsf(rel) > cone);
-                    const bool away = !(3.14159265f - fabsf(rel) > cone) && !(fabsf(rp) > 2e-3f);
-                    const bool take = inside && (n == 2 ? (away && !towards) : (windows ? towards : (towards || away)));
-                    const unsigned m = __ballot_sync(FULL, take);
-                    F110_CHECK(d.violations, !take || (fill + __popc(m & ((1u << lane) - 1u)) < 64 && i >= 0 && i < d.n_beams), F110_V_QUEUE);
-                    if (take) queue[wq][fill + __popc(m & ((1u << lane) - 1u))] = (k << 16) | i;
-                    fill += __popc(m);
-                    __syncwarp();
-                    if (fill >= 32) {
-                        agents_cast<SCAN_T>(d, rec, w0, blockIdx.x * AG_THREADS, queue[wq][lane]);
-                        __syncwarp();
-                        const int rest = queue[wq][32 + lane];
-                        __syncwarp();
-                        queue[wq][lane] = rest;
-                        fill -= 32;
-                        __syncwarp();
-                    }
-                }
-            }
-        }
-        if (lane < fill) agents_cast<SCAN_T>(d, rec, w0, blockIdx.x * AG_THREADS, queue[wq][lane]);
+        int fill = 0, unit = 0;
+        for (int k = 0; k < 32; k++)
+            agents_walk_record<SCAN_T, false>(d, rec, span, queue[wq], fill, w0 + k, k, w0, lane, a032, inc32, inv_inc32, unit, 1, 0);
+        if (lane < fill) agents_cast<SCAN_T, false>(d, rec, span, w0, queue[wq][lane]);
         __syncwarp();
     }
+}
+
+template <typename SCAN_T>
+// 8 CTAs of 128 threads per SM (64 registers, 240 bytes of spill): measured on config 4 (131 072 agents) against the compiler's own
+// choice (96 registers, 5 CTAs) and 6 / 10 / 12 CTAs: step 1.887 ms against 1.937 / 1.951 / 1.937 / 1.991 (profiles/r2g_agents_occupancy_ab.json)
+__global__ void __launch_bounds__(AG_THREADS, 8) k_agents(const F110Dev d)
+{
+    __shared__ double rec[11][AG_THREADS];
+    __shared__ int span[6][AG_THREADS];
+    __shared__ int queue[AG_THREADS / 32][64];
+    const int ia = blockIdx.x * AG_THREADS + threadIdx.x;
+    agents_body<SCAN_T>(d, rec, span, queue, threadIdx.x, ia, ia < d.n_envs * d.n_agents);
 }
 
 void f110_launch_agents(const F110Dev &d, cudaStream_t st)
@@ -1048,7 +1089,7 @@ struct F110HostOut {
     double *obs;            // [10][N] or null
     double *scans;          // [N][B] or null
     uint8_t *done;          // [N] or null
-    double cmd[2];          // one env: its (steer, velocity) command, read by the host (has_cmd) -- saves the kernel a PCIe read
+    double cmd[16];         // one env of up to 8 agents: their (steer, velocity) commands, read by the host (has_cmd) -- saves the kernel a PCIe read
     int has_cmd;
 };
 
@@ -1173,11 +1214,139 @@ __global__ void __launch_bounds__(NT) k_step_fused64(const F110Dev d, const F110
     }
 }
 
+// The same for a handful of envs of 2 .. F110_FUSED_MULTI_MAX_AGENTS agents (the reference's head-to-head races through the drop-in
+// F110Env: five launches and their gaps were 80 us per step of a two-agent env): a CTA of 32 warps per env.  Threads 0 .. A-1
+// integrate the agents and prepare their scans, the warps cast the A scans (rounds claimed per scan, a warp starts on scan
+// warp % A and moves on to the others), threads 0 .. A-1 apply the iTTC outcomes, warp 0 runs k_agents' body (GJK on the
+// pre-iTTC poses, opponent casts into the scans), thread 0 the lap bookkeeping, and the CTA writes the observation to the
+// caller's mapped host buffers.  Order and device functions are those of k_dynamics -> k_raycast64 -> k_agents -> k_finalize.
+template <bool ROT, bool POW2>
+__global__ void __launch_bounds__(1024) k_step_fused_multi64(const F110Dev d, const F110HostOut ho)
+{
+    __shared__ Scan64 rows[F110_FUSED_MULTI_MAX_AGENTS];
+    __shared__ int next_round[F110_FUSED_MULTI_MAX_AGENTS], hit_any[F110_FUSED_MULTI_MAX_AGENTS], active;
+    __shared__ double rec[11][AG_THREADS];      // a column per (agent, opponent) pair: A (A - 1) <= 56
+    __shared__ int span[6][AG_THREADS];
+    __shared__ int queue[32][64];
+    __shared__ unsigned char pair_hit[F110_FUSED_MULTI_MAX_AGENTS][F110_FUSED_MULTI_MAX_AGENTS];
+    const int e = (int)blockIdx.x, A = d.n_agents, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t NA = (size_t)d.n_envs * A;
+    PHASE(0);
+    if (tid == 0) active = !(d.step_mask && !d.step_mask[e]);
+    if (tid < A) {
+        const int ia = e * A + tid;
+        if (!(d.step_mask && !d.step_mask[e])) {
+            dynamics_agent(d, ia, ho.has_cmd ? ho.cmd + 2 * tid : nullptr);
+            PHASE(1);
+            prepare_env_scan64<ROT, POW2>(d, ia, &rows[tid], true);
+            PHASE(2);
+        }
+        next_round[tid] = 0;
+        hit_any[tid] = 0;
+    }
+    __syncthreads();
+    if (!active) return;
+    unsigned nlook = 0;
+    for (int k = 0; k < A; k++) {
+        int s2 = warp % A + k;
+        if (s2 >= A) s2 -= A;
+        bool h = false;
+        scan_rounds_claimed<ROT, POW2, true, false>(d, rows + s2, h, nlook, &next_round[s2], false);
+        if (__any_sync(FULL, h) && lane == 0) atomicOr(&hit_any[s2], 1);
+    }
+    PHASE(3);
+    __syncthreads();
+    if (tid < A) {       // RaceCar.check_ttc (base_classes.py:241-250)
+        PHASE(4);
+        const size_t ia = (size_t)e * A + tid;
+        const bool h = hit_any[tid] != 0;
+        if (h) { d.state[3 * NA + ia] = 0.; d.state[4 * NA + ia] = 0.; d.state[5 * NA + ia] = 0.; d.state[6 * NA + ia] = 0.; }
+        d.in_collision[ia] = h ? 1 : 0;
+    }
+    __syncthreads();
+    // k_agents' work spread over the CTA.  Its scalar part is a chain of fp64 divisions, atan2 and GJK per agent and opponent
+    // (33 us for two agents in the lanes of one warp): here a thread per (agent, opponent) pair writes that pair's record,
+    // threads 64 .. run GJK on the A (A - 1) / 2 pairs beside them, then all 32 warps walk all records, each taking every 32nd
+    // 32-beam step, and cast their candidates -- records of one agent at the same time, hence the atomic minimum.
+    {
+        const int P = A * (A - 1);
+        if (tid < P) {
+            const int a = tid / (A - 1);
+            int o = tid - a * (A - 1);
+            if (o >= a) o++;
+            const size_t ia = (size_t)e * A + a;
+            const double px = d.state[ia], py = d.state[NA + ia], yaw = d.state[4 * NA + ia];
+            const double len = d.params[F110_NP * a + F110_P_LENGTH], wid = d.params[F110_NP * a + F110_P_WIDTH];
+            double esn, ecs;
+            sincos(yaw, &esn, &ecs);
+            agent_pair_record(d, rec, span, tid, (int)ia, (size_t)e * A, o, px, py, yaw, atan2(esn, ecs), len, wid);
+        } else if (tid >= 64 && tid < 64 + P / 2) {
+            // Simulator.check_collision (base_classes.py:529-543): a thread per unordered pair i < j, as collision_multiple
+            // visits them (collision_models.py:185-212), instead of agent_collision's loop over every partner per agent
+            int q = tid - 64, i = 0;
+            while (q >= A - 1 - i) { q -= A - 1 - i; i++; }
+            const int j = i + 1 + q;
+            const size_t ii = (size_t)e * A + i, jj = (size_t)e * A + j;
+            const double gw = d.params[F110_NP * A + 0], gl = d.params[F110_NP * A + 1];
+            double vi[4][2], vj[4][2];
+            get_vertices(d.pose_pre[ii], d.pose_pre[NA + ii], d.pose_pre[2 * NA + ii], gl, gw, vi);
+            get_vertices(d.pose_pre[jj], d.pose_pre[NA + jj], d.pose_pre[2 * NA + jj], gl, gw, vj);
+            const bool c = gjk_collision(vi, vj);
+            pair_hit[i][j] = c; pair_hit[j][i] = c;
+        }
+        __syncthreads();
+        if (tid < A) {      // collision_idx = last writer = largest partner that collides
+            int last = -1;
+            for (int o = 0; o < A; o++)
+                if (o != tid && pair_hit[tid][o]) last = o;
+            const size_t ia = (size_t)e * A + tid;
+            d.collision_idx[ia] = (double)last;
+            d.collisions[ia] = (last >= 0 || d.in_collision[ia]) ? 1.0 : 0.0;
+        }
+        const float a032 = (float)__ldg(d.scan_angles), inc32 = (float)(d.fov / (double)(d.n_beams - 1)), inv_inc32 = 1.0f / inc32;
+        int fill = 0, unit = 0;
+        for (int p = 0; p < P; p++)
+            agents_walk_record<double, true>(d, rec, span, queue[warp], fill, p, p, 0, lane, a032, inc32, inv_inc32, unit, 32, warp);
+        if (lane < fill) agents_cast<double, true>(d, rec, span, 0, queue[warp][lane]);
+    }
+    PHASE(5);
+    __syncthreads();
+    if (tid == 0) {
+        PHASE(7);
+        finalize_env(d, e);
+        if (ho.done) ho.done[e] = d.done[e];
+    }
+    if (ho.scans) {
+        const double *src = (const double *)d.scans + (size_t)e * A * d.n_beams;
+        double *dst = ho.scans + (size_t)e * A * d.n_beams;
+        for (int i = tid; i < A * d.n_beams; i += 1024) dst[i] = src[i];
+    }
+    if (ho.obs) {
+        __syncthreads();      // collisions, lap times and counts of finalize_env
+        for (int i = tid; i < 10 * A; i += 1024) {
+            const size_t at = (size_t)(i / A) * NA + (size_t)e * A + (size_t)(i % A);
+            ho.obs[at] = d.state[at];          // obs_block = state | collisions | lap_times | lap_counts
+        }
+    }
+    PHASE(6);
+}
+
 void f110_launch_step_fused64(const F110Dev &d, double *obs_host, double *scans_host, uint8_t *done_host, const double *cmd_host, int variant,
                               cudaStream_t st)
 {
-    F110HostOut ho = { obs_host, scans_host, done_host, { 0., 0. }, 0 };
-    if (cmd_host && d.n_envs == 1) { ho.cmd[0] = cmd_host[0]; ho.cmd[1] = cmd_host[1]; ho.has_cmd = 1; }
+    F110HostOut ho;
+    memset(&ho, 0, sizeof(ho));
+    ho.obs = obs_host; ho.scans = scans_host; ho.done = done_host;
+    if (cmd_host && d.n_envs == 1 && d.n_agents <= 8) {
+        for (int k = 0; k < 2 * d.n_agents; k++) ho.cmd[k] = cmd_host[k];
+        ho.has_cmd = 1;
+    }
+    if (d.n_agents > 1) {
+        if (d.has_rot) k_step_fused_multi64<true, false><<<d.n_envs, 1024, 0, st>>>(d, ho);
+        else if (d.res_pow2) k_step_fused_multi64<false, true><<<d.n_envs, 1024, 0, st>>>(d, ho);
+        else k_step_fused_multi64<false, false><<<d.n_envs, 1024, 0, st>>>(d, ho);
+        return;
+    }
     const bool cnt = d.count_lookups != 0;
     const bool wide = d.n_envs <= d.n_sm && !(variant & 1);        // variant bit 0: always 256 threads per env
 #define FUSED(R, P)                                                                   \

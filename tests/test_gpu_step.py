@@ -388,8 +388,8 @@ def test_step_host_small_batch_paths_agree(dtype, agents):
             assert (np.asarray(got["obs"]).reshape(ref_obs.shape) == ref_obs).all(), t
             assert (np.asarray(got["scans"]) == ref_scans).all(), t
             assert (np.asarray(got["done"]).astype(bool) == ref_done.astype(bool)).all(), t
-    if dtype == "fp64" and agents == 1:
-        # a handful of single-agent fp64 envs: the whole tick, export included, is ONE kernel (k_step_fused64)
+    if dtype == "fp64":
+        # a handful of fp64 envs: the whole tick, export included, is ONE kernel (k_step_fused64 / k_step_fused_multi64)
         assert (envs[1].launch_count - launches0[1]) == (envs[2].launch_count - launches0[2]) == T
     else:
         # the mapped path really ran: one more launch per step (k_export_host) than the copy path
@@ -450,6 +450,58 @@ def test_fused_step_is_bit_identical_to_the_three_kernel_step(N, yaw):
     assert a.lookups() == b.lookups()
     # one launch per step against three (four with the host export)
     assert a.launch_count - la < (b.launch_count - lb) / 2.5
+
+
+@pytest.mark.parametrize("N,A", [(1, 2), (1, 4), (5, 8), (148, 2), (40, 3)])
+def test_fused_multi_agent_step_is_bit_identical_to_the_step_kernel_by_kernel(N, A):
+    """Up to F110_FUSED_MULTI_MAX_ENVS envs of 2 .. 8 agents (fp64) are stepped by one kernel as well (k_step_fused_multi64:
+    dynamics -> scans -> iTTC -> GJK + opponent casts -> lap bookkeeping -> host export) -- the reference's head-to-head races
+    through the drop-in F110Env; raycast_variant=256 keeps the five launches.  Same device functions: bit-identical through
+    f110_step and f110_step_host (mapped and pageable buffers), masked resets and auto-resets; cars start on top of each other so
+    that GJK, opponent casts and iTTC all fire."""
+    from red_gym_b200 import BatchF110Env
+    from red_gym_b200.host import raceline_poses
+    import torch
+    rng = np.random.default_rng(100 * N + A)
+    poses = np.repeat(raceline_poses(N)[:, None, :], A, axis=1)
+    poses[:, 1:, 0] += rng.uniform(-2.0, 2.0, (N, A - 1))
+    poses[:, 1:, 1] += rng.uniform(-2.0, 2.0, (N, A - 1))
+    poses[:, 1:, 2] = rng.uniform(-3, 3, (N, A - 1))
+    kw = dict(num_envs=N, num_agents=A, map=os.path.join(MAPS, "example_map"), auto_reset=True, reset_poses=poses[: max(1, N // 2)], ego_idx=A - 1)
+    a, b = BatchF110Env(**kw), BatchF110Env(raycast_variant=256, **kw)
+    a.reset(poses); b.reset(poses)
+    la, lb = a.launch_count, b.launch_count
+    act_h = torch.zeros((N, A, 2), dtype=torch.float64).pin_memory()
+    bufs = [dict(obs=torch.zeros((10, N, A), dtype=torch.float64).pin_memory(), scans=torch.zeros((N, A, 1080), dtype=torch.float64).pin_memory(),
+                 done=torch.zeros((N,), dtype=torch.uint8).pin_memory()) for _ in range(2)]
+    pag = dict(obs=np.zeros((10, N, A)), scans=np.zeros((N, A, 1080)), done=np.zeros((N,), dtype=np.uint8))
+    gjk = blocked = 0
+    for t in range(75):
+        act = np.stack([rng.uniform(-0.4, 0.4, (N, A)), rng.uniform(0.0, 7.0, (N, A))], axis=-1)
+        if t % 3 == 0:
+            a.step(act); b.step(act)
+        elif t % 3 == 1:
+            act_h.numpy()[...] = act
+            a.step_host(act_h, bufs[0]["obs"], bufs[0]["scans"], bufs[0]["done"])
+            b.step_host(act_h, bufs[1]["obs"], bufs[1]["scans"], bufs[1]["done"])
+            for k in ("obs", "scans", "done"):
+                assert torch.equal(bufs[0][k], bufs[1][k]), (t, k)
+            assert torch.equal(bufs[0]["scans"].cuda(), a.scans) and torch.equal(bufs[0]["obs"].cuda(), a.obs_block)
+        else:
+            a.step_host(act, pag["obs"], pag["scans"], pag["done"])
+            b.step(act)
+            assert (pag["scans"] == b.scans.cpu().numpy()).all() and (pag["obs"] == b.obs_block.cpu().numpy()).all()
+            assert (pag["done"].astype(bool) == b.done.cpu().numpy().astype(bool)).all()
+        if t == 40 and N > 1:
+            mask = np.arange(N) % 2 == 0
+            a.reset(poses, mask=mask); b.reset(poses, mask=mask)
+        assert torch.equal(a.obs_block, b.obs_block) and torch.equal(a.scans, b.scans), t
+        assert torch.equal(a.collision_idx, b.collision_idx) and torch.equal(a.in_collision, b.in_collision)
+        assert torch.equal(a.done, b.done) and torch.equal(a.toggle_list, b.toggle_list) and torch.equal(a.noise_step, b.noise_step)
+        gjk += int((a.collision_idx >= 0).sum())
+    assert torch.equal(a.episode_count, b.episode_count)
+    assert gjk > 0 or N * A < 10
+    assert a.launch_count - la < (b.launch_count - lb) / 3.5          # one launch per step against five (six with the host export)
 
 
 def test_sharded_run_is_bit_identical_to_unsharded():
