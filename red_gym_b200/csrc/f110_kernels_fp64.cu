@@ -1237,9 +1237,7 @@ __global__ void __launch_bounds__(1024) k_step_fused_multi64(const F110Dev d, co
         const int ia = e * A + tid;
         if (!(d.step_mask && !d.step_mask[e])) {
             dynamics_agent(d, ia, ho.has_cmd ? ho.cmd + 2 * tid : nullptr);
-            PHASE(1);
             prepare_env_scan64<ROT, POW2>(d, ia, &rows[tid], true);
-            PHASE(2);
         }
         next_round[tid] = 0;
         hit_any[tid] = 0;
@@ -1295,6 +1293,7 @@ __global__ void __launch_bounds__(1024) k_step_fused_multi64(const F110Dev d, co
             pair_hit[i][j] = c; pair_hit[j][i] = c;
         }
         __syncthreads();
+        PHASE(1);
         if (tid < A) {      // collision_idx = last writer = largest partner that collides
             int last = -1;
             for (int o = 0; o < A; o++)
@@ -1307,6 +1306,7 @@ __global__ void __launch_bounds__(1024) k_step_fused_multi64(const F110Dev d, co
         int fill = 0, unit = 0;
         for (int p = 0; p < P; p++)
             agents_walk_record<double, true>(d, rec, span, queue[warp], fill, p, p, 0, lane, a032, inc32, inv_inc32, unit, 32, warp);
+        PHASE(2);
         if (lane < fill) agents_cast<double, true>(d, rec, span, 0, queue[warp][lane]);
     }
     PHASE(5);

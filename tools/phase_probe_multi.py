@@ -8,9 +8,9 @@ import torch
 from red_gym_b200 import BatchF110Env, MAPS_DIR, _native
 lib = _native.load()
 lib.f110_debug_phases.argtypes = [ctypes.c_void_p]
-names = ["dynamics (threads 0..A-1)", "scan preparation", "barrier + rounds of warp 0", "barrier: the other warps' rounds",
-         "iTTC outcome + barrier + GJK / opponent casts (warp 0)", "barrier", "lap bookkeeping + export"]
-order = [0, 1, 2, 3, 4, 5, 7, 6]
+names = ["dynamics + prep + rounds of warp 0", "barrier: other warps' rounds", "iTTC + pair records + GJK + barrier", "walk all records (+ full batches)",
+         "last batch cast", "barrier", "lap bookkeeping + export"]
+order = [0, 3, 4, 1, 2, 5, 7, 6]
 for A in (2, 4):
     env = BatchF110Env(num_envs=1, num_agents=A, map=os.path.join(MAPS_DIR, "example_map"), dtype="fp64", noise="numpy")
     env.reset(np.array([[[0.7 + 1.2 * a, 0.0, 1.37079632679] for a in range(A)]]))
