@@ -79,8 +79,8 @@ for k in range(K):
     if worst_far > 0.02: msg.append("%.1f %% of the beams beyond 0.15 m" % (100 * worst_far))
     if worst_state > 5e-2: msg.append("states of agreeing envs apart by %.3g" % worst_state)
     findings += bool(msg)
-    print("config %2d: A %d N %4d B %4d fov %.3f %-5s dt %.3f %-11s T %2d  flags differ %.2f %%  beams > 2 cm %.2f %%  state %.2g  %s"
-          % (k, A, N, B, fov, integ, dt, m, T, 100 * frac_diff, 100 * worst_scan, worst_state, "; ".join(msg) or "ok"), flush=True)
+    print("config %2d: A %d N %4d B %4d fov %.3f %-5s dt %.3f %-11s T %2d  flags differ %.2f %%  beams > 2 cm %.2f %% > 15 cm %.2f %%  state %.2g  %s"
+          % (k, A, N, B, fov, integ, dt, m, T, 100 * frac_diff, 100 * worst_scan, 100 * worst_far, worst_state, "; ".join(msg) or "ok"), flush=True)
     for e in [e64] + e32:
         e.close()
 L = _native.load()
