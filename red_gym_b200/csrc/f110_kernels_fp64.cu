@@ -889,8 +889,8 @@ static __device__ __forceinline__ void agent_pair_record(const F110Dev &d, doubl
 template <typename SCAN_T, bool ATOMIC>
 static __device__ __forceinline__ void agents_walk_record(const F110Dev &d, const double (*rec)[AG_THREADS], const int (*span)[AG_THREADS],
                                                           int *queue_w, int &fill, int s, int code, int w0, int lane, float a032, float inc32,
-                                                          float inv_inc32, int &unit, int n_units, int my_unit)
-{
+                                                          float inv_inc32, int &unit, int n_units, int my_unit, int cast_at = 32)
+{   // cast_at: queue fill at which a batch of 32 is cast on the spot (the queue holds cast_at + 32 entries)
     const int first = span[0][s], lastb = span[1][s];
     if (first > lastb) return;
     const float off = __int_as_float(span[2][s]), cone = __int_as_float(span[3][s]), par = __int_as_float(span[4][s]);
@@ -924,16 +924,20 @@ static __device__ __forceinline__ void agents_walk_record(const F110Dev &d, cons
             const bool away = !(3.14159265f - fabsf(rel) > cone) && !(fabsf(rp) > 2e-3f);
             const bool take = inside && (n == 2 ? (away && !towards) : (windows ? towards : (towards || away)));
             const unsigned m = __ballot_sync(FULL, take);
-            F110_CHECK(d.violations, !take || (fill + __popc(m & ((1u << lane) - 1u)) < 64 && i >= 0 && i < d.n_beams), F110_V_QUEUE);
+            F110_CHECK(d.violations, !take || (fill + __popc(m & ((1u << lane) - 1u)) < cast_at + 32 && i >= 0 && i < d.n_beams), F110_V_QUEUE);
             if (take) queue_w[fill + __popc(m & ((1u << lane) - 1u))] = (code << 16) | i;
             fill += __popc(m);
             __syncwarp();
-            if (fill >= 32) {
+            if (fill >= cast_at) {
                 agents_cast<SCAN_T, ATOMIC>(d, rec, span, w0, queue_w[lane]);
                 __syncwarp();
-                const int rest = queue_w[32 + lane];
-                __syncwarp();
-                queue_w[lane] = rest;
+                for (int q0 = 0; q0 + 32 < fill; q0 += 32) {       // move the rest down, 32 entries at a time (cast_at = 32: once)
+                    const int q = q0 + lane;
+                    const int rest = q + 32 < fill ? queue_w[32 + q] : 0;
+                    __syncwarp();
+                    if (q + 32 < fill) queue_w[q] = rest;
+                    __syncwarp();
+                }
                 fill -= 32;
                 __syncwarp();
             }
@@ -1227,7 +1231,7 @@ __global__ void __launch_bounds__(1024) k_step_fused_multi64(const F110Dev d, co
     __shared__ int next_round[F110_FUSED_MULTI_MAX_AGENTS], hit_any[F110_FUSED_MULTI_MAX_AGENTS], active;
     __shared__ double rec[11][AG_THREADS];      // a column per (agent, opponent) pair: A (A - 1) <= 56
     __shared__ int span[6][AG_THREADS];
-    __shared__ int queue[32][64];
+    __shared__ int queue[32][128], fills[32];
     __shared__ unsigned char pair_hit[F110_FUSED_MULTI_MAX_AGENTS][F110_FUSED_MULTI_MAX_AGENTS];
     const int e = (int)blockIdx.x, A = d.n_agents, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t NA = (size_t)d.n_envs * A;
@@ -1264,8 +1268,8 @@ __global__ void __launch_bounds__(1024) k_step_fused_multi64(const F110Dev d, co
     __syncthreads();
     // k_agents' work spread over the CTA.  Its scalar part is a chain of fp64 divisions, atan2 and GJK per agent and opponent
     // (33 us for two agents in the lanes of one warp): here a thread per (agent, opponent) pair writes that pair's record,
-    // threads 64 .. run GJK on the A (A - 1) / 2 pairs beside them, then all 32 warps walk all records, each taking every 32nd
-    // 32-beam step, and cast their candidates -- records of one agent at the same time, hence the atomic minimum.
+    // threads 64 .. run GJK on the A (A - 1) / 2 pairs beside them, then a warp per record queues its candidate beams and all 32
+    // warps cast them, a batch of 32 each -- records of one agent at the same time, hence the atomic minimum.
     {
         const int P = A * (A - 1);
         if (tid < P) {
@@ -1304,10 +1308,20 @@ __global__ void __launch_bounds__(1024) k_step_fused_multi64(const F110Dev d, co
         }
         const float a032 = (float)__ldg(d.scan_angles), inc32 = (float)(d.fov / (double)(d.n_beams - 1)), inv_inc32 = 1.0f / inc32;
         int fill = 0, unit = 0;
-        for (int p = 0; p < P; p++)
-            agents_walk_record<double, true>(d, rec, span, queue[warp], fill, p, p, 0, lane, a032, inc32, inv_inc32, unit, 32, warp);
+        for (int p = warp; p < P; p += 32)       // a warp per record (every warp walking every record cost 2 700 cycles per record)
+            agents_walk_record<double, true>(d, rec, span, queue[warp], fill, p, p, 0, lane, a032, inc32, inv_inc32, unit, 1, 0, 96);
         PHASE(2);
-        if (lane < fill) agents_cast<double, true>(d, rec, span, 0, queue[warp][lane]);
+        // the candidates sit in the queues of the warps that walked a record: level them -- batch b of the CTA's candidates, in
+        // queue order, is cast by warp b mod 32
+        if (lane == 0) fills[warp] = fill;
+        __syncthreads();
+        int total = 0;
+        for (int w = 0; w < 32; w++) total += fills[w];
+        for (int g = 32 * warp + lane; g < ((total + 31) & ~31); g += 1024) {
+            int w = 0, before = 0;
+            while (w < 31 && before + fills[w] <= g) { before += fills[w]; w++; }
+            if (g < total) agents_cast<double, true>(d, rec, span, 0, queue[w][g - before]);
+        }
     }
     PHASE(5);
     __syncthreads();
