@@ -137,9 +137,9 @@ class BatchF110Env(object):
             return
         target = int(rows) if exact else max(int(rows), self._noise_rows + 128)
         if self._noise_rng is None:
-            self._noise_rng = np.random.default_rng(seed=self.seed)
-        new = self._noise_rng.normal(0., 0.01, size=(target - self._noise_rows, self.num_beams))
-        nat.check(self.lib.f110_set_noise_rows(self._h, _hp(np.ascontiguousarray(new)), self._noise_rows, new.shape[0], self._stream()))
+            self._noise_rng = host.NoiseRowsAhead(self.seed, self.num_beams)       # the rows are drawn ahead by a helper thread
+        new = self._noise_rng.take(target - self._noise_rows)
+        nat.check(self.lib.f110_set_noise_rows(self._h, _hp(new), self._noise_rows, new.shape[0], self._stream()))
         self._noise_rows = target
 
     def _wrap_buffers(self):
@@ -397,6 +397,10 @@ class BatchF110Env(object):
         self._torch.cuda.synchronize(self.device)
 
     def close(self):
+        ahead = getattr(self, "_noise_rng", None)
+        if ahead is not None:
+            ahead.close()
+            self._noise_rng = None
         rh = getattr(self, "_render_h", None)
         if rh:
             self.lib.f110_render_destroy(rh)

@@ -618,7 +618,13 @@ extern "C" int f110_set_noise_rows(f110_sim *s, const double *rows, int64_t firs
     const size_t B = s->d.n_beams;
     long long need = first_row + n_rows;
     if (need > s->noise_cap) {
-        long long cap = s->noise_cap ? s->noise_cap : 256;
+        // the first table holds 64 MB of rows (7767 steps at 1080 beams; at least 256, at most 8192 rows): growing it means a
+        // stream synchronisation, cudaMalloc and cudaFree in the middle of a rollout, measured at 5 ... 146 ms on this pool
+        long long cap = s->noise_cap;
+        if (!cap) {
+            cap = (long long)((64ull << 20) / (B * 8));
+            cap = cap < 256 ? 256 : (cap > 8192 ? 8192 : cap);
+        }
         while (cap < need) cap *= 2;
         double *nn = nullptr;
         CK(cudaStreamSynchronize(st));

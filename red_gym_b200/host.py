@@ -230,3 +230,58 @@ def bind_to_gpu_numa(device_index):
         return cpus
     except Exception:
         return None
+
+
+class NoiseRowsAhead(object):
+    """The parity-mode noise stream, drawn ahead of the steps by a helper thread (pure numpy: no CUDA call leaves the caller's
+    thread).  Row k is the k-th `default_rng(seed).normal(0, 0.01, B)` of a car since its reset (base_classes.py:202,
+    laser_models.py:451); a (count, B) draw fills row by row, so chunks of rows are the same numbers as successive B-draws.
+    PCG64 + ziggurat is sequential -- 17 us per row of 1080 normals, a third of a single-env step when drawn in the stepping
+    thread -- but numpy releases the GIL while it fills, so a second thread keeps two chunks ready.  take(n) returns the
+    next n rows of the stream, in order, waiting for the helper only if the caller outruns it."""
+    CHUNK = 128
+
+    def __init__(self, seed, num_beams, std=0.01):
+        import queue
+        import threading
+        self._rng = np.random.default_rng(seed=seed)
+        self._beams, self._std = int(num_beams), float(std)
+        self._q = queue.Queue(maxsize=2)
+        self._stop = threading.Event()
+        self._left = None
+        self._threaded = os.environ.get("F110_NOISE_AHEAD", "1") != "0"      # 0: draw in the caller's thread, at take()
+        if self._threaded:
+            self._t = threading.Thread(target=self._run, name="f110-noise-rows", daemon=True)
+            self._t.start()
+
+    def _run(self):
+        import queue
+        while not self._stop.is_set():
+            rows = self._rng.normal(0., self._std, size=(self.CHUNK, self._beams))
+            while not self._stop.is_set():
+                try:
+                    self._q.put(rows, timeout=0.2)
+                    break
+                except queue.Full:
+                    pass
+
+    def take(self, n):
+        parts, have = [], 0
+        if self._left is not None:
+            parts.append(self._left); have = self._left.shape[0]; self._left = None
+        while have < n:
+            rows = self._q.get() if self._threaded else self._rng.normal(0., self._std, size=(max(n - have, 1), self._beams))
+            parts.append(rows); have += rows.shape[0]
+        out = parts[0] if len(parts) == 1 else np.concatenate(parts, axis=0)
+        if have > n:
+            self._left = out[n:]
+            out = out[:n]
+        return np.ascontiguousarray(out)
+
+    def close(self):
+        self._stop.set()
+        try:
+            while True:
+                self._q.get_nowait()
+        except Exception:
+            pass

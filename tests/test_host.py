@@ -60,3 +60,17 @@ def test_start_rotation():
     r = host.start_rotation(np.array([0.3]))
     th = 0.3
     assert (r[0] == np.array([np.cos(-th), -np.sin(-th), np.sin(-th), np.cos(-th)])).all()
+
+
+def test_noise_rows_drawn_ahead_are_the_streams_rows():
+    """NoiseRowsAhead (parity-mode noise drawn by a helper thread): whatever the sizes asked for, the rows are the successive
+    `default_rng(seed).normal(0, 0.01, B)` draws of the reference (base_classes.py:202, laser_models.py:451)."""
+    from red_gym_b200.host import NoiseRowsAhead
+    for seed, B in ((12345, 1080), (7, 33)):
+        ahead = NoiseRowsAhead(seed, B)
+        sizes = [128, 1, 300, 127, 2, 700]
+        got = np.concatenate([ahead.take(n) for n in sizes], axis=0)
+        ahead.close()
+        rng = np.random.default_rng(seed=seed)
+        want = np.stack([rng.normal(0., 0.01, size=B) for _ in range(sum(sizes))])
+        assert got.shape == want.shape and (got == want).all()
