@@ -253,6 +253,7 @@ class NoiseRowsAhead(object):
         if self._threaded:
             self._t = threading.Thread(target=self._run, name="f110-noise-rows", daemon=True)
             self._t.start()
+            _live_noise_threads.add(self)
 
     def _run(self):
         import queue
@@ -278,10 +279,25 @@ class NoiseRowsAhead(object):
             out = out[:n]
         return np.ascontiguousarray(out)
 
-    def close(self):
+    def close(self, join=False):
         self._stop.set()
         try:
             while True:
                 self._q.get_nowait()
         except Exception:
             pass
+        if join and self._threaded:
+            self._t.join(timeout=1.0)
+
+
+# helper threads still alive at interpreter exit are stopped and joined first: a daemon thread that comes back from numpy
+# for the GIL while the interpreter is being torn down is the one thing that could go wrong with them
+import atexit      # noqa: E402
+import weakref     # noqa: E402
+_live_noise_threads = weakref.WeakSet()
+
+
+@atexit.register
+def _stop_noise_threads():
+    for a in list(_live_noise_threads):
+        a.close(join=True)
