@@ -836,25 +836,23 @@ static __device__ __forceinline__ void agent_collision(const F110Dev &d, int ia,
 // (px, py, yaw) -- own pose AFTER the iTTC zeroing, the opponent's from before it, drawn with THIS agent's length / width --
 // into column t: rec = px, py, yaw, corner x / y * 4; span = first / last blocked beam (get_blocked_view_indices,
 // laser_models.py:283-315), float bits of bearing offset, cone, edge offset; scanning agent
-static __device__ __forceinline__ void agent_pair_record(const F110Dev &d, double (*rec)[AG_THREADS], int (*span)[AG_THREADS], int t, int ia,
-                                                         size_t base, int o, double px, double py, double yaw, double ego_ang, double len, double wid)
+// get_blocked_view_indices (laser_models.py:283-315), one corner: the beam nearest to its bearing
+static __device__ __forceinline__ int corner_beam(const F110Dev &d, double cx, double cy, double px, double py, double ego_ang)
 {
-    const int NA = d.n_envs * d.n_agents;
-    double v[4][2];
-    get_vertices(d.pose_pre[base + o], d.pose_pre[NA + base + o], d.pose_pre[2 * (size_t)NA + base + o], len, wid, v);
-    int mn = 0x7fffffff, mx = -1;
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-        double vx = v[k][0] - px, vy = v[k][1] - py;
-        double nrm = sqrt(vx * vx + vy * vy);
-        double angle = ego_ang - atan2(vy / nrm, vx / nrm);
-        if (angle > PI_()) angle = angle - 2 * PI_();
-        else if (angle < -PI_()) angle = angle + 2 * PI_();
-        int b = nearest_beam(d, -angle);
-        mn = min(mn, b); mx = max(mx, b);
-        rec[3 + 2 * k][t] = v[k][0];
-        rec[4 + 2 * k][t] = v[k][1];
-    }
+    double vx = cx - px, vy = cy - py;
+    double nrm = sqrt(vx * vx + vy * vy);
+    double angle = ego_ang - atan2(vy / nrm, vx / nrm);
+    if (angle > PI_()) angle = angle - 2 * PI_();
+    else if (angle < -PI_()) angle = angle + 2 * PI_();
+    return nearest_beam(d, -angle);
+}
+
+// the rest of a record once the corners v and the first / last blocked beam are known: pose, float bits of bearing offset,
+// cone and edge offset for the beam tests (a) and (b) above, scanning agent
+static __device__ __forceinline__ void pair_record_tail(const F110Dev &d, double (*rec)[AG_THREADS], int (*span)[AG_THREADS], int t, int ia,
+                                                        const double v[4][2], int mn, int mx, double yaw_o, double px, double py, double yaw,
+                                                        double len, double wid)
+{
     rec[0][t] = px; rec[1][t] = py; rec[2][t] = yaw;
     // (a): bearing of the centre relative to scan angle 0 and the half angle of the bounding circle; (b): edge directions
     const double cx = 0.25 * (((v[0][0] + v[1][0]) + v[2][0]) + v[3][0]) - px;
@@ -863,7 +861,6 @@ static __device__ __forceinline__ void agent_pair_record(const F110Dev &d, doubl
     const float R = 0.5f * sqrtf((float)(len * len + wid * wid)) * 1.0001f;
     double off = yaw - (double)atan2f((float)cy, (float)cx);
     off -= 2 * PI_() * rint(off / (2 * PI_()));
-    const double yaw_o = d.pose_pre[2 * (size_t)NA + base + o];
     double par = yaw - yaw_o;
     par -= PI_() / 2 * rint(par / (PI_() / 2));
     float cone = (dist > 1.001f * R) ? asinf(R / dist) + 2e-3f : 4.0f;   // inside the circle (or NaN): every beam
@@ -880,6 +877,49 @@ static __device__ __forceinline__ void agent_pair_record(const F110Dev &d, doubl
     span[3][t] = __float_as_int(cone);
     span[4][t] = __float_as_int((float)par);      // NaN: every beam counts as parallel
     span[5][t] = ia;
+}
+
+// RaceCar.ray_cast_agents, the part per (agent, opponent): the record of opponent o (agent base + o) as seen by agent ia at
+// (px, py, yaw) -- own pose AFTER the iTTC zeroing, the opponent's from before it, drawn with THIS agent's length / width --
+// into column t: rec = px, py, yaw, corner x / y * 4; span = first / last blocked beam, the beam tests' constants, agent
+static __device__ __forceinline__ void agent_pair_record(const F110Dev &d, double (*rec)[AG_THREADS], int (*span)[AG_THREADS], int t, int ia,
+                                                         size_t base, int o, double px, double py, double yaw, double ego_ang, double len, double wid)
+{
+    const int NA = d.n_envs * d.n_agents;
+    double v[4][2];
+    const double yaw_o = d.pose_pre[2 * (size_t)NA + base + o];
+    get_vertices(d.pose_pre[base + o], d.pose_pre[NA + base + o], yaw_o, len, wid, v);
+    int mn = 0x7fffffff, mx = -1;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int b = corner_beam(d, v[k][0], v[k][1], px, py, ego_ang);
+        mn = min(mn, b); mx = max(mx, b);
+        rec[3 + 2 * k][t] = v[k][0];
+        rec[4 + 2 * k][t] = v[k][1];
+    }
+    pair_record_tail(d, rec, span, t, ia, v, mn, mx, yaw_o, px, py, yaw, len, wid);
+}
+
+// the same by four neighbouring lanes (lane & 3 = corner; `group` = the ballot of the lanes that take part, whole groups of
+// four): the four corner bearings -- square root, two divisions, atan2 and the nearest-beam search each, 3 500 cycles -- side
+// by side instead of one after the other (19 000 of the 38 000 cycles of a two-agent single-env tick)
+static __device__ __forceinline__ void agent_pair_record4(const F110Dev &d, double (*rec)[AG_THREADS], int (*span)[AG_THREADS], int t, int ia,
+                                                          size_t base, int o, double px, double py, double yaw, double ego_ang, double len, double wid,
+                                                          unsigned group)
+{
+    const int NA = d.n_envs * d.n_agents, k = threadIdx.x & 3;
+    double v[4][2];
+    const double yaw_o = d.pose_pre[2 * (size_t)NA + base + o];
+    get_vertices(d.pose_pre[base + o], d.pose_pre[NA + base + o], yaw_o, len, wid, v);
+    const double cx = k == 0 ? v[0][0] : k == 1 ? v[1][0] : k == 2 ? v[2][0] : v[3][0];
+    const double cy = k == 0 ? v[0][1] : k == 1 ? v[1][1] : k == 2 ? v[2][1] : v[3][1];
+    const int b = corner_beam(d, cx, cy, px, py, ego_ang);
+    int mn = b, mx = b;
+    mn = min(mn, __shfl_xor_sync(group, mn, 1)); mx = max(mx, __shfl_xor_sync(group, mx, 1));
+    mn = min(mn, __shfl_xor_sync(group, mn, 2)); mx = max(mx, __shfl_xor_sync(group, mx, 2));
+    rec[3 + 2 * k][t] = cx;
+    rec[4 + 2 * k][t] = cy;
+    if (k == 0) pair_record_tail(d, rec, span, t, ia, v, mn, mx, yaw_o, px, py, yaw, len, wid);
 }
 
 // ray_cast (laser_models.py:318-346) over the candidate beams of record s (item code `code`: s = w0 + code): the calling warp
@@ -1267,25 +1307,26 @@ __global__ void __launch_bounds__(1024) k_step_fused_multi64(const F110Dev d, co
     }
     __syncthreads();
     // k_agents' work spread over the CTA.  Its scalar part is a chain of fp64 divisions, atan2 and GJK per agent and opponent
-    // (33 us for two agents in the lanes of one warp): here a thread per (agent, opponent) pair writes that pair's record,
-    // threads 64 .. run GJK on the A (A - 1) / 2 pairs beside them, then a warp per record queues its candidate beams and all 32
+    // (33 us for two agents in the lanes of one warp): here four threads per (agent, opponent) pair write that pair's record,
+    // threads 256 .. run GJK on the A (A - 1) / 2 pairs beside them, then a warp per record queues its candidate beams and all 32
     // warps cast them, a batch of 32 each -- records of one agent at the same time, hence the atomic minimum.
     {
         const int P = A * (A - 1);
-        if (tid < P) {
-            const int a = tid / (A - 1);
-            int o = tid - a * (A - 1);
+        const unsigned group = __ballot_sync(FULL, tid < 4 * P);        // four lanes per pair: threads 0 .. 4 P - 1 (at most 224)
+        if (tid < 4 * P) {
+            const int p = tid >> 2, a = p / (A - 1);
+            int o = p - a * (A - 1);
             if (o >= a) o++;
             const size_t ia = (size_t)e * A + a;
             const double px = d.state[ia], py = d.state[NA + ia], yaw = d.state[4 * NA + ia];
             const double len = d.params[F110_NP * a + F110_P_LENGTH], wid = d.params[F110_NP * a + F110_P_WIDTH];
             double esn, ecs;
             sincos(yaw, &esn, &ecs);
-            agent_pair_record(d, rec, span, tid, (int)ia, (size_t)e * A, o, px, py, yaw, atan2(esn, ecs), len, wid);
-        } else if (tid >= 64 && tid < 64 + P / 2) {
+            agent_pair_record4(d, rec, span, p, (int)ia, (size_t)e * A, o, px, py, yaw, atan2(esn, ecs), len, wid, group);
+        } else if (tid >= 256 && tid < 256 + P / 2) {
             // Simulator.check_collision (base_classes.py:529-543): a thread per unordered pair i < j, as collision_multiple
             // visits them (collision_models.py:185-212), instead of agent_collision's loop over every partner per agent
-            int q = tid - 64, i = 0;
+            int q = tid - 256, i = 0;
             while (q >= A - 1 - i) { q -= A - 1 - i; i++; }
             const int j = i + 1 + q;
             const size_t ii = (size_t)e * A + i, jj = (size_t)e * A + j;
