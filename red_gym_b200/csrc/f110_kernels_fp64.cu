@@ -1261,9 +1261,10 @@ __global__ void __launch_bounds__(NT) k_step_fused64(const F110Dev d, const F110
 // The same for a handful of envs of 2 .. F110_FUSED_MULTI_MAX_AGENTS agents (the reference's head-to-head races through the drop-in
 // F110Env: five launches and their gaps were 80 us per step of a two-agent env): a CTA of 32 warps per env.  Threads 0 .. A-1
 // integrate the agents and prepare their scans, the warps cast the A scans (rounds claimed per scan, a warp starts on scan
-// warp % A and moves on to the others), threads 0 .. A-1 apply the iTTC outcomes, warp 0 runs k_agents' body (GJK on the
-// pre-iTTC poses, opponent casts into the scans), thread 0 the lap bookkeeping, and the CTA writes the observation to the
-// caller's mapped host buffers.  Order and device functions are those of k_dynamics -> k_raycast64 -> k_agents -> k_finalize.
+// warp % A and moves on to the others), threads 0 .. A-1 apply the iTTC outcomes, k_agents' work is spread over the CTA (GJK
+// on the pre-iTTC poses per pair, opponent records by four threads each, their candidate beams cast by all warps: see below),
+// thread 0 does the lap bookkeeping, and the CTA writes the observation to the caller's mapped host buffers.  Order and
+// device functions are those of k_dynamics -> k_raycast64 -> k_agents -> k_finalize (46 us per call for two agents).
 template <bool ROT, bool POW2>
 __global__ void __launch_bounds__(1024) k_step_fused_multi64(const F110Dev d, const F110HostOut ho)
 {
